@@ -1,0 +1,186 @@
+/*
+ * TEST INFRASTRUCTURE ONLY -- CPU restatement of the reference block-tridiagonal PCG.
+ *
+ * This file is included twice by pcg_oracle.c, once with T=float (SUF=f32) and once
+ * with T=double (SUF=f64).  It is never linked into the product library.
+ *
+ * It restates, on the host and for one problem at a time:
+ *   - the compressed block-tridiagonal block-row mat-vec     reference include/utils.cuh:46-85  (bdmv)
+ *   - the 3*nx halo window of a vector                       reference include/utils.cuh:9-40   (loadbdVec)
+ *   - the PCG recurrence, exit test and outputs              reference include/pcg.cuh:118-212
+ *   - (order==1 only) the shared-memory tree reduction order reference GLASS/src/L1/reduce.cuh:35-62, 64-96
+ *                                                            and the dot of GLASS/src/L1/dot.cuh:49-60
+ *
+ * Parity pinning: the reference ships no golden vectors or tests; this
+ * restatement is pinned against (a) the hand-derived C1 known answers (tests/golden/c1_kat.json)
+ * and (b) outputs of the reference CUDA kernel itself, compiled unmodified from
+ * /root/reference by oracle/Makefile into oracle/_ref/ and run on a B200
+ * (tests/golden/ref_cuda_*.npz, generator oracle/make_ref_fixtures.py).
+ */
+
+#define CAT_(a, b) a##_##b
+#define CAT(a, b) CAT_(a, b)
+#define FN(name) CAT(name, SUF)
+
+/* y_b = M_b . [x_{b-1} | x_b | x_{b+1}], accumulating columns in ascending order like
+ * bdmv (utils.cuh:58-84): block 0 skips its left block, block N-1 skips its right block,
+ * so the padding blocks of the layout are never touched. */
+static void FN(blockrow_mv)(const T *M, const T *x, T *y, uint32_t nx, uint32_t N, uint32_t b)
+{
+    const T *Mb = M + (size_t)b * 3u * nx * nx;
+    uint32_t c_lo = (b == 0) ? nx : 0;
+    uint32_t c_hi = (b == N - 1) ? 2u * nx : 3u * nx;
+    for (uint32_t r = 0; r < nx; r++) {
+        T acc = (T)0;
+        for (uint32_t c = c_lo; c < c_hi; c++) {
+            /* window column c maps to global vector element (b-1)*nx + c */
+            acc += Mb[(size_t)nx * c + r] * x[(size_t)b * nx + c - nx];
+        }
+        y[(size_t)b * nx + r] = acc;
+    }
+}
+
+void FN(oracle_bdmv)(const T *M, const T *x, T *y, uint32_t nx, uint32_t N)
+{
+    for (uint32_t b = 0; b < N; b++) FN(blockrow_mv)(M, x, y, nx, N, b);
+}
+
+/* GLASS tree reduction, in place (reduce.cuh:35-62).  Sequential emulation: within one
+ * halving step the reads x[i+s] are of elements no thread writes in that step, so a plain
+ * ascending loop reproduces the parallel result; the odd tail is folded into x[0] after
+ * x[0]'s own add (same thread, program order). */
+static T FN(glass_reduce)(T *x, uint32_t n)
+{
+    uint32_t s = n;
+    while (s > 3) {
+        uint32_t odd = s & 1u;
+        s = (s - odd) / 2u;
+        for (uint32_t i = 0; i < s; i++) x[i] += x[i + s];
+        if (odd) x[0] += x[2u * s];
+    }
+    for (uint32_t i = 1; i < s; i++) x[0] += x[i];
+    return x[0];
+}
+
+/* Global dot product a.b over N blocks of nx.
+ * order 0: plain left-to-right accumulation (the "straightforward host oracle").
+ * order 1: reference order -- per block dot via glass::dot (products then tree), then
+ *          the N per-block partials through the same tree (pcg.cuh:144-148,163-168,187-192). */
+static T FN(dot)(const T *a, const T *b, uint32_t nx, uint32_t N, int order, T *scratch)
+{
+    if (order == 0) {
+        T acc = (T)0;
+        for (size_t i = 0; i < (size_t)nx * N; i++) acc += a[i] * b[i];
+        return acc;
+    }
+    T *part = scratch;            /* N entries  */
+    T *blk = scratch + N;         /* nx entries */
+    for (uint32_t k = 0; k < N; k++) {
+        for (uint32_t i = 0; i < nx; i++) blk[i] = a[(size_t)k * nx + i] * b[(size_t)k * nx + i];
+        part[k] = FN(glass_reduce)(blk, nx);
+    }
+    return FN(glass_reduce)(part, N);
+}
+
+/*
+ * One PCG solve.  Pinv == NULL means identity preconditioner (r_tilde = r).
+ * lambda is in/out (warm start).  Returns 0, or -1 on bad arguments / allocation failure.
+ * eta_trace (nullable, capacity max_iter+1) receives eta_0, eta'_1, ... for diagnostics.
+ * Follows pcg.cuh:118-212 line by line:
+ *   r = gamma - S lambda ; rt = Pinv r ; p = rt ; eta = r.rt
+ *   loop: ups = S p ; alpha = eta/(p.ups) ; lambda += alpha p ; r -= alpha ups ;
+ *         rt = Pinv r ; eta' = r.rt ; if |eta'| < tol {iter++; exit=false; break}
+ *         beta = eta'/eta ; eta = eta' ; p = rt + beta p
+ */
+int FN(oracle_pcg)(const T *S, const T *Pinv, const T *gamma, T *lambda,
+                   uint32_t nx, uint32_t N, T exit_tol, uint32_t max_iter, int order,
+                   uint32_t *iters_out, int *max_iter_exit_out, T *eta_trace)
+{
+    if (!S || !gamma || !lambda || nx == 0 || N < 2) return -1;
+    size_t n = (size_t)nx * N;
+    T *buf = (T *)malloc(sizeof(T) * (4 * n + N + nx));
+    if (!buf) return -1;
+    T *r = buf, *rt = buf + n, *p = buf + 2 * n, *ups = buf + 3 * n, *scratch = buf + 4 * n;
+
+    FN(oracle_bdmv)(S, lambda, r, nx, N);
+    for (size_t i = 0; i < n; i++) r[i] = gamma[i] - r[i];
+    if (Pinv) FN(oracle_bdmv)(Pinv, r, rt, nx, N);
+    else memcpy(rt, r, sizeof(T) * n);
+    memcpy(p, rt, sizeof(T) * n);
+    T eta = FN(dot)(r, rt, nx, N, order, scratch);
+    if (eta_trace) eta_trace[0] = eta;
+
+    uint32_t iter;
+    int max_iter_exit = 1;
+    for (iter = 0; iter < max_iter; iter++) {
+        FN(oracle_bdmv)(S, p, ups, nx, N);
+        T v = FN(dot)(p, ups, nx, N, order, scratch);
+        T alpha = eta / v;
+        for (size_t i = 0; i < n; i++) {
+            lambda[i] += alpha * p[i];
+            r[i] -= alpha * ups[i];
+        }
+        if (Pinv) FN(oracle_bdmv)(Pinv, r, rt, nx, N);
+        else memcpy(rt, r, sizeof(T) * n);
+        T eta_new = FN(dot)(r, rt, nx, N, order, scratch);
+        if (eta_trace) eta_trace[iter + 1] = eta_new;
+        if (FABS(eta_new) < exit_tol) { iter++; max_iter_exit = 0; break; }
+        T beta = eta_new / eta;
+        eta = eta_new;
+        for (size_t i = 0; i < n; i++) p[i] = rt[i] + beta * p[i];
+    }
+    if (iters_out) *iters_out = iter;
+    if (max_iter_exit_out) *max_iter_exit_out = max_iter_exit;
+    free(buf);
+    return 0;
+}
+
+/* ---- batched driver over a pthread pool: problem i uses slabs at i*3*N*nx^2 / i*N*nx ---- */
+typedef struct {
+    const T *S, *Pinv, *gamma;
+    T *lambda;
+    uint32_t nx, N, batch, max_iter;
+    T tol;
+    int order;
+    uint32_t *iters;
+    uint8_t *exits;
+    volatile uint32_t *next;
+} FN(batch_job);
+
+static void *FN(batch_worker)(void *arg)
+{
+    FN(batch_job) *j = (FN(batch_job) *)arg;
+    size_t ms = (size_t)3 * j->N * j->nx * j->nx, vs = (size_t)j->N * j->nx;
+    for (;;) {
+        uint32_t i = __atomic_fetch_add(j->next, 1u, __ATOMIC_RELAXED);
+        if (i >= j->batch) break;
+        uint32_t it = 0;
+        int ex = 0;
+        FN(oracle_pcg)(j->S + i * ms, j->Pinv ? j->Pinv + i * ms : NULL, j->gamma + i * vs,
+                       j->lambda + i * vs, j->nx, j->N, j->tol, j->max_iter, j->order, &it, &ex, NULL);
+        if (j->iters) j->iters[i] = it;
+        if (j->exits) j->exits[i] = (uint8_t)ex;
+    }
+    return NULL;
+}
+
+int FN(oracle_pcg_batched)(const T *S, const T *Pinv, const T *gamma, T *lambda,
+                           uint32_t nx, uint32_t N, uint32_t batch, T exit_tol, uint32_t max_iter,
+                           int order, uint32_t *iters, uint8_t *exits, int threads)
+{
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    volatile uint32_t next = 0;
+    FN(batch_job) job = {S, Pinv, gamma, lambda, nx, N, batch, max_iter, exit_tol, order, iters, exits, &next};
+    pthread_t th[256];
+    int started = 0;
+    for (int t = 1; t < threads; t++)
+        if (pthread_create(&th[started], NULL, FN(batch_worker), &job) == 0) started++;
+    FN(batch_worker)(&job);
+    for (int t = 0; t < started; t++) pthread_join(th[t], NULL);
+    return 0;
+}
+
+#undef FN
+#undef CAT
+#undef CAT_
