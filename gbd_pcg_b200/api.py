@@ -1,0 +1,212 @@
+"""Python mirror of the reference host interface, over the C ABI (include/gbdpcg.h).
+
+Same names and argument meaning as the reference's templates so that tests read like calls into
+the reference:
+
+    solvePCG(h_S, h_gamma, h_lambda, stateSize, knotPoints, config)        reference include/interface.cuh:24-89
+    solvePCG(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda,
+             d_r, d_p, d_v_temp, d_eta_new_temp, config)                    reference include/interface.cuh:92-144
+    pcg_solve(...)                                                          reference README.md:42 (same as the first form)
+    pcg_config(exit_tol, max_iter, grid, block, empty_pinv)                 reference include/types.cuh:18-35
+
+Host arrays are numpy; device arrays are anything with ``data_ptr()`` (torch CUDA tensors).
+PyTorch is used only as a device-memory / stream provider; all arithmetic is in libgbdpcg.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _lib
+from ._lib import Config, GbdpcgError, PlanInfo  # noqa: F401  (re-exported)
+
+DEFAULT_MAX_PCG_ITER = 25      # reference include/constants.cuh:15
+DEFAULT_EPSILON = 1e-6         # reference include/constants.cuh:17
+DEFAULT_GRID = (128, 1, 1)     # reference include/constants.cuh:18 (carried, ignored -- as in the reference)
+DEFAULT_BLOCK = (64, 1, 1)     # reference include/constants.cuh:19 (carried, ignored -- as in the reference)
+
+
+@dataclass
+class pcg_config:
+    """Field-for-field mirror of reference ``pcg_config<T>`` (include/types.cuh:18-35)."""
+    pcg_exit_tol: float = DEFAULT_EPSILON
+    pcg_max_iter: int = DEFAULT_MAX_PCG_ITER
+    pcg_grid: tuple = DEFAULT_GRID
+    pcg_block: tuple = DEFAULT_BLOCK
+    empty_pinv: int = 1
+    # extensions (not in the reference): launch tuning knobs of the C ABI
+    flags: int = field(default=0, repr=False)
+    cluster: int = field(default=0, repr=False)
+
+    def to_c(self) -> Config:
+        return Config(float(self.pcg_exit_tol), int(self.pcg_max_iter), int(self.empty_pinv), int(self.flags), int(self.cluster))
+
+
+def _suffix(dtype) -> str:
+    dtype = np.dtype(dtype)
+    if dtype == np.float32:
+        return "f32"
+    if dtype == np.float64:
+        return "f64"
+    raise TypeError(f"T must be float or double (reference templates), got {dtype}")
+
+
+def _host(a, dtype, n, name, writable=False):
+    if not isinstance(a, np.ndarray) or a.dtype != dtype or not a.flags.c_contiguous or a.size < n:
+        raise ValueError(f"{name}: need a C-contiguous numpy array of {np.dtype(dtype)} with at least {n} elements")
+    if writable and not a.flags.writeable:
+        raise ValueError(f"{name}: must be writable")
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def _dev_ptr(t, name, nullable=False):
+    if t is None:
+        if nullable:
+            return None
+        raise ValueError(f"{name} must not be None")
+    if isinstance(t, int):
+        return C.c_void_p(t)
+    if hasattr(t, "is_cuda"):
+        if not t.is_cuda or not t.is_contiguous():
+            raise ValueError(f"{name}: need a contiguous CUDA tensor")
+        return C.c_void_p(t.data_ptr())
+    raise TypeError(f"{name}: need a CUDA tensor or an integer device address")
+
+
+def _torch_dtype_suffix(t):
+    import torch
+    if t.dtype == torch.float32:
+        return "f32"
+    if t.dtype == torch.float64:
+        return "f64"
+    raise TypeError("T must be float32 or float64")
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return C.c_void_p(stream)
+    return C.c_void_p(stream.cuda_stream)
+
+
+# ------------------------------------------------------------------------------------------------
+# reference-shaped entry points
+# ------------------------------------------------------------------------------------------------
+def solvePCG(*args, **kw):
+    """Both reference overloads, selected like C++ would: 6 arguments = host pointers, 11 = device pointers."""
+    if args and isinstance(args[0], np.ndarray):
+        return _solve_host(*args, **kw)
+    if args and isinstance(args[0], (int, np.integer)):
+        return _solve_dev(*args, **kw)
+    raise TypeError("solvePCG: unrecognised overload (first argument must be h_S or state_size)")
+
+
+def pcg_solve(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None):
+    """README.md:42 spelling; config defaults like the README's ``default_config``."""
+    return _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config, h_Pinv=h_Pinv)
+
+
+def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None, return_flag=False):
+    """Host-pointer overload.  ``h_lambda`` is updated in place; returns the iteration count
+    (the reference returns 1 unconditionally, include/interface.cuh:88 -- a defect this build does not keep).
+    ``h_Pinv`` (extension) supplies Phi^-1; it is used only when ``config.empty_pinv == 0``."""
+    config = config or pcg_config()
+    if not config.empty_pinv and h_Pinv is None:
+        # the reference prints this and carries on with an uninitialised d_Pinv (interface.cuh:33-34,45-46)
+        print("This api can only be called with no preconditioner")
+    suf = _suffix(h_S.dtype)
+    nx, N = int(stateSize), int(knotPoints)
+    ms, vs = 3 * N * nx * nx, N * nx
+    cfg = config.to_c()
+    if h_Pinv is None:
+        cfg.empty_pinv = 1
+    it, ex = C.c_uint32(0), C.c_int32(0)
+    f = getattr(_lib.lib(), f"gbdpcg_solve_host_{suf}")
+    _lib.check(f(None, _host(h_S, h_S.dtype, ms, "h_S"),
+                 None if h_Pinv is None else _host(h_Pinv, h_S.dtype, ms, "h_Pinv"),
+                 _host(h_gamma, h_S.dtype, vs, "h_gamma"), _host(h_lambda, h_S.dtype, vs, "h_lambda", True),
+                 nx, N, C.byref(cfg), C.byref(it), C.byref(ex)))
+    return (it.value, bool(ex.value)) if return_flag else it.value
+
+
+def _solve_dev(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_r=None, d_p=None, d_v_temp=None,
+               d_eta_new_temp=None, config=None, stream=None, return_flag=False):
+    """Device-pointer overload (blocking, returns iterations like include/interface.cuh:136,143).
+    The four scratch buffers of the reference are accepted and ignored.  ``d_Pinv`` is always applied,
+    whatever ``config.empty_pinv`` says, because the reference kernel has no notion of that flag
+    (it is passed as a 13th launch argument to a 12-parameter kernel, interface.cuh:126 vs pcg.cuh:56-68);
+    ``d_Pinv=None`` (extension) selects the identity."""
+    config = config or pcg_config()
+    suf = _torch_dtype_suffix(d_S)
+    cfg = config.to_c()
+    cfg.empty_pinv = 1 if d_Pinv is None else 0
+    it, ex = C.c_uint32(0), C.c_int32(0)
+    f = getattr(_lib.lib(), f"gbdpcg_solve_dev_sync_{suf}")
+    _lib.check(f(None, _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv", True), _dev_ptr(d_gamma, "d_gamma"),
+                 _dev_ptr(d_lambda, "d_lambda"), int(state_size), int(knot_points), C.byref(cfg),
+                 C.byref(it), C.byref(ex), _stream_ptr(stream)))
+    return (it.value, bool(ex.value)) if return_flag else it.value
+
+
+# ------------------------------------------------------------------------------------------------
+# asynchronous / batched forms (extensions)
+# ------------------------------------------------------------------------------------------------
+def solve_dev_async(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, config, d_iters=None, d_exit=None, stream=None):
+    """Enqueue one solve on ``stream`` and return immediately (d_iters: uint32[1], d_exit: uint8[1], optional)."""
+    suf = _torch_dtype_suffix(d_S)
+    cfg = config.to_c()
+    if d_Pinv is None:
+        cfg.empty_pinv = 1
+    f = getattr(_lib.lib(), f"gbdpcg_solve_dev_{suf}")
+    _lib.check(f(None, _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv", True), _dev_ptr(d_gamma, "d_gamma"),
+                 _dev_ptr(d_lambda, "d_lambda"), int(state_size), int(knot_points), C.byref(cfg),
+                 _dev_ptr(d_iters, "d_iters", True), _dev_ptr(d_exit, "d_exit", True), _stream_ptr(stream)))
+
+
+def solve_batched_dev(state_size, knot_points, batch, d_S, d_Pinv, d_gamma, d_lambda, config, d_iters=None, d_exit=None,
+                      stream=None):
+    """Enqueue ``batch`` independent solves (problem-major slabs) on ``stream``."""
+    suf = _torch_dtype_suffix(d_S)
+    cfg = config.to_c()
+    if d_Pinv is None:
+        cfg.empty_pinv = 1
+    f = getattr(_lib.lib(), f"gbdpcg_solve_batched_dev_{suf}")
+    _lib.check(f(None, _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv", True), _dev_ptr(d_gamma, "d_gamma"),
+                 _dev_ptr(d_lambda, "d_lambda"), int(state_size), int(knot_points), int(batch), C.byref(cfg),
+                 _dev_ptr(d_iters, "d_iters", True), _dev_ptr(d_exit, "d_exit", True), _stream_ptr(stream)))
+
+
+def solve_batched_host(h_S, h_Pinv, h_gamma, h_lambda, state_size, knot_points, batch, config):
+    """Blocking batched solve on host arrays (pageable or pinned).  Returns (iters[batch], max_iter_exit[batch])."""
+    suf = _suffix(h_S.dtype)
+    nx, N, B = int(state_size), int(knot_points), int(batch)
+    ms, vs = 3 * N * nx * nx * B, N * nx * B
+    cfg = config.to_c()
+    if h_Pinv is None:
+        cfg.empty_pinv = 1
+    iters = np.zeros(B, dtype=np.uint32)
+    exits = np.zeros(B, dtype=np.uint8)
+    f = getattr(_lib.lib(), f"gbdpcg_solve_batched_host_{suf}")
+    _lib.check(f(None, _host(h_S, h_S.dtype, ms, "h_S"),
+                 None if h_Pinv is None else _host(h_Pinv, h_S.dtype, ms, "h_Pinv"),
+                 _host(h_gamma, h_S.dtype, vs, "h_gamma"), _host(h_lambda, h_S.dtype, vs, "h_lambda", True),
+                 nx, N, B, C.byref(cfg), iters.ctypes.data_as(C.c_void_p), exits.ctypes.data_as(C.c_void_p)))
+    return iters, exits.astype(bool)
+
+
+def plan_query(state_size, knot_points, dtype=np.float32, has_pinv=True, config=None) -> dict:
+    """What the library would launch for this shape (replaces pcgSharedMemSize / checkPcgOccupancy,
+    reference include/pcg.cuh:13-49)."""
+    info = PlanInfo()
+    cfg = (config or pcg_config()).to_c()
+    _lib.check(_lib.lib().gbdpcg_plan_query(int(state_size), int(knot_points), int(np.dtype(dtype) == np.float64),
+                                            int(bool(has_pinv)), C.byref(cfg), C.byref(info)))
+    return {k: (getattr(info, k).decode() if k == "kernel" else getattr(info, k)) for k, _ in PlanInfo._fields_}
+
+
+def kernel_launches() -> int:
+    return int(_lib.lib().gbdpcg_kernel_launches())

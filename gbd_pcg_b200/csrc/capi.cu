@@ -1,0 +1,566 @@
+// capi.cu -- host side of libgbdpcg.so: launch planning, workspaces and the extern "C" entry points
+// declared in include/gbdpcg.h.  Replaces the host templates of the reference
+// (include/interface.cuh:24-144) and its occupancy helper (include/pcg.cuh:13-49).
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "gbdpcg.h"
+#include "kernel_table.h"
+#include "pcg_generic.cuh"
+#include "pcg_rows.cuh"
+
+namespace gbdpcg {
+
+// ------------------------------------------------------------------------------------------------
+// errors
+// ------------------------------------------------------------------------------------------------
+static thread_local std::string tl_error;
+static thread_local int tl_cuda_error = 0;
+static std::atomic<uint64_t> g_launches{0};
+
+static int fail(int status, const char *fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    tl_error = buf;
+    return status;
+}
+static int fail_cuda(cudaError_t e, const char *what, int line)
+{
+    tl_cuda_error = (int)e;
+    return fail(GBDPCG_ERR_CUDA, "CUDA error %d (%s) in %s at capi.cu:%d", (int)e, cudaGetErrorString(e), what, line);
+}
+#define CK(call)                                                         \
+    do {                                                                 \
+        cudaError_t e__ = (call);                                        \
+        if (e__ != cudaSuccess) return fail_cuda(e__, #call, __LINE__);  \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// launch planning
+// ------------------------------------------------------------------------------------------------
+static constexpr size_t kMaxDynSmem = 227 * 1024;  // sm_100: 227 KB opt-in dynamic shared memory per CTA
+
+struct Plan {
+    bool generic = false;
+    const RowsVariant *v = nullptr;
+    int cluster = 1, bpc = 0, threads = 0, nbuf = 1, pmode = P_NONE;
+    size_t smem = 0;
+    const void *fn = nullptr;
+    const char *name = "";
+};
+
+static void all_variants(bool f64, int nx, const RowsVariant **tab, int *cnt)
+{
+    *tab = nullptr;
+    *cnt = 0;
+    switch (nx) {
+#define CASE(NX) \
+    case NX: *tab = f64 ? rows_variants_f64_##NX(cnt) : rows_variants_f32_##NX(cnt); break;
+        GBDPCG_FOR_EACH_NX(CASE)
+#undef CASE
+        default: break;
+    }
+}
+
+template <typename T>
+static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
+{
+    return make_smem_plan<T>(v->nx, v->nxp, v->sb, bpc, nbuf).total;
+}
+
+template <typename T>
+static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+{
+    constexpr bool f64 = sizeof(T) == 8;
+    const RowsVariant *tab;
+    int cnt;
+    all_variants(f64, (int)nx, &tab, &cnt);
+    if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
+        static const int cl_opts[] = {1, 2, 4, 8, 16};
+        for (int cl : cl_opts) {
+            if (cfg.cluster && (int)cfg.cluster != cl) continue;
+            const int bpc = ((int)N + cl - 1) / cl;
+            const int threads = round_up(bpc * (int)nx, 32);
+            // Phi^-1 placement preference: registers, then shared memory
+            int pm_opts[2] = {P_REG, P_SMEM};
+            int n_pm = 2;
+            if (!has_p) { pm_opts[0] = P_NONE; n_pm = 1; }
+            else if (cfg.flags & GBDPCG_FLAG_PINV_SMEM) { pm_opts[0] = P_SMEM; n_pm = 1; }
+            else if (cfg.flags & GBDPCG_FLAG_PINV_REG) { n_pm = 1; }
+            for (int ip = 0; ip < n_pm; ip++) {
+                for (int i = 0; i < cnt; i++) {
+                    const RowsVariant *v = &tab[i];
+                    if (v->clustered != (cl > 1) || v->pmode != pm_opts[ip] || threads > v->maxt) continue;
+                    int nbuf = (v->pmode == P_NONE) ? 1 : 2;
+                    size_t smem = rows_smem<T>(v, bpc, nbuf);
+                    if (smem > kMaxDynSmem && nbuf == 2) { nbuf = 1; smem = rows_smem<T>(v, bpc, 1); }
+                    if (smem > kMaxDynSmem) continue;
+                    out->generic = false; out->v = v; out->cluster = cl; out->bpc = bpc; out->threads = threads;
+                    out->nbuf = nbuf; out->pmode = v->pmode; out->smem = smem; out->fn = v->fn; out->name = v->name;
+                    return GBDPCG_OK;
+                }
+            }
+        }
+        if (cfg.cluster || (cfg.flags & (GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_PINV_REG)))
+            return fail(GBDPCG_ERR_UNSUPPORTED, "no register-row kernel fits nx=%u N=%u %s with the forced cluster=%u flags=0x%x",
+                        nx, N, f64 ? "f64" : "f32", cfg.cluster, cfg.flags);
+    }
+    // runtime-nx fallback: one CTA, vectors in shared memory
+    const size_t smem = generic_smem_bytes<T>(nx, N);
+    if (smem > kMaxDynSmem)
+        return fail(GBDPCG_ERR_UNSUPPORTED, "system nx=%u N=%u %s needs %zu B of shared memory in the fallback kernel (limit %zu)",
+                    nx, N, f64 ? "f64" : "f32", smem, kMaxDynSmem);
+    out->generic = true; out->v = nullptr; out->cluster = 1; out->bpc = (int)N;
+    const int rows = (int)(nx * N);
+    out->threads = rows >= 1024 ? 1024 : round_up(rows, 32);
+    out->nbuf = 0; out->pmode = has_p ? 3 : 0; out->smem = smem;
+    out->fn = has_p ? (const void *)pcg_generic_kernel<T, true> : (const void *)pcg_generic_kernel<T, false>;
+    out->name = has_p ? (f64 ? "pcg_generic<f64,P>" : "pcg_generic<f32,P>") : (f64 ? "pcg_generic<f64,I>" : "pcg_generic<f32,I>");
+    return GBDPCG_OK;
+}
+
+// per-(device, kernel) one-time attribute setup + occupancy
+struct FnState { const void *fn; int device; int clustered; };
+static std::mutex g_fn_mu;
+static std::vector<FnState> g_fn_ready;
+struct OccState { const void *fn; int device, cluster, threads; size_t smem; int resident; };
+static std::vector<OccState> g_occ;
+
+static int prepare_fn(const void *fn, bool clustered)
+{
+    int dev;
+    CK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_fn_mu);
+    for (auto &s : g_fn_ready)
+        if (s.fn == fn && s.device == dev) return GBDPCG_OK;
+    CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
+    if (clustered) CK(cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    g_fn_ready.push_back({fn, dev, clustered});
+    return GBDPCG_OK;
+}
+
+static int max_resident_problems(const Plan &p, int *out)
+{
+    int dev, sms;
+    CK(cudaGetDevice(&dev));
+    {
+        std::lock_guard<std::mutex> lk(g_fn_mu);
+        for (auto &o : g_occ)
+            if (o.fn == p.fn && o.device == dev && o.cluster == p.cluster && o.threads == p.threads && o.smem == p.smem) {
+                *out = o.resident;
+                return GBDPCG_OK;
+            }
+    }
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (p.cluster == 1) {
+        int per_sm = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p.fn, p.threads, p.smem));
+        *out = per_sm * sms;
+    } else {
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3(p.cluster);
+        lc.blockDim = dim3(p.threads);
+        lc.dynamicSmemBytes = p.smem;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = p.cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        lc.attrs = at; lc.numAttrs = 1;
+        int ncl = 0;
+        CK(cudaOccupancyMaxActiveClusters(&ncl, p.fn, &lc));
+        *out = ncl;
+    }
+    std::lock_guard<std::mutex> lk(g_fn_mu);
+    g_occ.push_back({p.fn, dev, p.cluster, p.threads, p.smem, *out});
+    return GBDPCG_OK;
+}
+
+template <typename T>
+static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lambda, uint32_t nx, uint32_t N,
+                  uint32_t batch, const gbdpcg_config &cfg, uint32_t *d_iters, uint8_t *d_exits, cudaStream_t stream)
+{
+    if (batch == 0) return GBDPCG_OK;
+    int rc = prepare_fn(p.fn, p.cluster > 1);
+    if (rc) return rc;
+    int resident = 0;
+    rc = max_resident_problems(p, &resident);
+    if (rc) return rc;
+    if (resident < 1)
+        return fail(GBDPCG_ERR_UNSUPPORTED, "kernel %s cannot become resident (cluster=%d threads=%d smem=%zu)", p.name, p.cluster,
+                    p.threads, p.smem);
+    const uint32_t n_groups = batch < (uint32_t)resident ? batch : (uint32_t)resident;
+
+    KernelArgs<T> a;
+    a.S = S; a.Pinv = P; a.gamma = gamma; a.lambda = lambda; a.iters = d_iters; a.exits = d_exits;
+    a.mat_stride = 3ull * N * nx * nx; a.vec_stride = (unsigned long long)N * nx;
+    a.N = N; a.batch = batch; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg.max_iter; a.two_buffers = (p.nbuf == 2);
+    a.tol = (T)cfg.exit_tol;
+
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3(n_groups * (uint32_t)p.cluster);
+    lc.blockDim = dim3(p.threads);
+    lc.dynamicSmemBytes = p.smem;
+    lc.stream = stream;
+    cudaLaunchAttribute at[1];
+    if (p.cluster > 1) {
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = p.cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        lc.attrs = at; lc.numAttrs = 1;
+    }
+    if (p.generic) {
+        uint32_t nxv = nx;
+        void *args[] = {&a, &nxv};
+        CK(cudaLaunchKernelExC(&lc, p.fn, args));
+    } else {
+        void *args[] = {&a};
+        CK(cudaLaunchKernelExC(&lc, p.fn, args));
+    }
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
+static int check_args(const void *S, const void *gamma, const void *lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg)
+{
+    if (!S || !gamma || !lambda) return fail(GBDPCG_ERR_INVALID, "S, gamma and lambda must not be NULL");
+    if (!cfg) return fail(GBDPCG_ERR_INVALID, "config must not be NULL");
+    if (nx == 0) return fail(GBDPCG_ERR_INVALID, "state size must be > 0");
+    if (N < 2) return fail(GBDPCG_ERR_INVALID, "knot points must be >= 2 (the reference reads block 1 unconditionally, utils.cuh:21-25)");
+    if (cfg->cluster && cfg->cluster != 1 && cfg->cluster != 2 && cfg->cluster != 4 && cfg->cluster != 8 && cfg->cluster != 16)
+        return fail(GBDPCG_ERR_INVALID, "config.cluster must be 0,1,2,4,8 or 16");
+    if ((uint64_t)nx * N > (1u << 24)) return fail(GBDPCG_ERR_UNSUPPORTED, "system too large");
+    return GBDPCG_OK;
+}
+
+}  // namespace gbdpcg
+
+// ------------------------------------------------------------------------------------------------
+// workspace
+// ------------------------------------------------------------------------------------------------
+struct gbdpcg_workspace {
+    int device = -1;
+    std::mutex mu;
+    cudaStream_t streams[2] = {nullptr, nullptr};
+    void *dbuf[4] = {nullptr, nullptr, nullptr, nullptr};  // S, Pinv, gamma, lambda
+    size_t dcap[4] = {0, 0, 0, 0};
+    uint32_t *d_iters = nullptr;
+    uint8_t *d_exits = nullptr;
+    size_t cap_batch = 0;
+    // mapped pinned scalars for the blocking single-solve calls: the kernel writes them in place
+    uint32_t *h_iters = nullptr;
+    uint8_t *h_exit = nullptr;
+    uint32_t *hd_iters = nullptr;
+    uint8_t *hd_exit = nullptr;
+};
+
+namespace gbdpcg {
+
+static int ws_init(gbdpcg_workspace *w)
+{
+    CK(cudaGetDevice(&w->device));
+    for (auto &s : w->streams) CK(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking));
+    void *h = nullptr;
+    CK(cudaHostAlloc(&h, 64, cudaHostAllocMapped));
+    w->h_iters = (uint32_t *)h;
+    w->h_exit = (uint8_t *)h + 32;
+    void *d = nullptr;
+    CK(cudaHostGetDevicePointer(&d, h, 0));
+    w->hd_iters = (uint32_t *)d;
+    w->hd_exit = (uint8_t *)d + 32;
+    return GBDPCG_OK;
+}
+
+static int ws_reserve(gbdpcg_workspace *w, int which, size_t bytes)
+{
+    if (w->dcap[which] >= bytes) return GBDPCG_OK;
+    if (w->dbuf[which]) { CK(cudaFree(w->dbuf[which])); w->dbuf[which] = nullptr; w->dcap[which] = 0; }
+    size_t cap = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&w->dbuf[which], cap);
+    if (e == cudaErrorMemoryAllocation) { cudaGetLastError(); return fail(GBDPCG_ERR_NOMEM, "cudaMalloc of %zu bytes failed", cap); }
+    if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc", __LINE__);
+    w->dcap[which] = cap;
+    return GBDPCG_OK;
+}
+
+static int ws_reserve_flags(gbdpcg_workspace *w, size_t batch)
+{
+    if (w->cap_batch >= batch) return GBDPCG_OK;
+    if (w->d_iters) { CK(cudaFree(w->d_iters)); w->d_iters = nullptr; }
+    if (w->d_exits) { CK(cudaFree(w->d_exits)); w->d_exits = nullptr; }
+    w->cap_batch = 0;
+    size_t cap = batch + batch / 4 + 64;
+    CK(cudaMalloc(&w->d_iters, cap * sizeof(uint32_t)));
+    CK(cudaMalloc(&w->d_exits, cap));
+    w->cap_batch = cap;
+    return GBDPCG_OK;
+}
+
+static void ws_release(gbdpcg_workspace *w)
+{
+    for (auto &b : w->dbuf) if (b) cudaFree(b);
+    if (w->d_iters) cudaFree(w->d_iters);
+    if (w->d_exits) cudaFree(w->d_exits);
+    if (w->h_iters) cudaFreeHost(w->h_iters);
+    for (auto &s : w->streams) if (s) cudaStreamDestroy(s);
+}
+
+// process-wide default workspaces, one per device
+static std::mutex g_ws_mu;
+static std::vector<gbdpcg_workspace *> g_default_ws;
+
+static int get_ws(gbdpcg_workspace *user, gbdpcg_workspace **out)
+{
+    if (user) { *out = user; return GBDPCG_OK; }
+    int dev;
+    CK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(g_ws_mu);
+    for (auto *w : g_default_ws)
+        if (w->device == dev) { *out = w; return GBDPCG_OK; }
+    auto *w = new gbdpcg_workspace();
+    int rc = ws_init(w);
+    if (rc) { ws_release(w); delete w; return rc; }
+    g_default_ws.push_back(w);
+    *out = w;
+    return GBDPCG_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// typed implementations
+// ------------------------------------------------------------------------------------------------
+static inline bool use_pinv(const void *Pinv, const gbdpcg_config *cfg) { return Pinv != nullptr && cfg->empty_pinv == 0; }
+
+template <typename T>
+static int solve_batched_dev(const T *S, const T *Pinv, const T *gamma, T *lambda, uint32_t nx, uint32_t N, uint32_t batch,
+                             const gbdpcg_config *cfg, uint32_t *d_iters, uint8_t *d_exits, void *stream)
+{
+    int rc = check_args(S, gamma, lambda, nx, N, cfg);
+    if (rc) return rc;
+    const bool has_p = use_pinv(Pinv, cfg);
+    Plan p;
+    rc = make_plan<T>(nx, N, has_p, *cfg, &p);
+    if (rc) return rc;
+    return launch<T>(p, S, has_p ? Pinv : nullptr, gamma, lambda, nx, N, batch, *cfg, d_iters, d_exits, (cudaStream_t)stream);
+}
+
+template <typename T>
+static int solve_dev_sync(gbdpcg_workspace *user_ws, const T *S, const T *Pinv, const T *gamma, T *lambda, uint32_t nx, uint32_t N,
+                          const gbdpcg_config *cfg, uint32_t *iters, int32_t *max_iter_exit, void *stream)
+{
+    gbdpcg_workspace *w;
+    int rc = get_ws(user_ws, &w);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(w->mu);
+    rc = solve_batched_dev<T>(S, Pinv, gamma, lambda, nx, N, 1, cfg, w->hd_iters, w->hd_exit, stream);
+    if (rc) return rc;
+    CK(cudaStreamSynchronize((cudaStream_t)stream));
+    if (iters) *iters = *(volatile uint32_t *)w->h_iters;
+    if (max_iter_exit) *max_iter_exit = *(volatile uint8_t *)w->h_exit;
+    return GBDPCG_OK;
+}
+
+template <typename T>
+static int solve_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const T *hg, T *hl, uint32_t nx, uint32_t N,
+                      const gbdpcg_config *cfg, uint32_t *iters, int32_t *max_iter_exit)
+{
+    int rc = check_args(hS, hg, hl, nx, N, cfg);
+    if (rc) return rc;
+    gbdpcg_workspace *w;
+    rc = get_ws(user_ws, &w);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(w->mu);
+    const bool has_p = use_pinv(hP, cfg);
+    const size_t mb = sizeof(T) * 3 * (size_t)N * nx * nx, vb = sizeof(T) * (size_t)N * nx;
+    if ((rc = ws_reserve(w, 0, mb))) return rc;
+    if (has_p && (rc = ws_reserve(w, 1, mb))) return rc;
+    if ((rc = ws_reserve(w, 2, vb))) return rc;
+    if ((rc = ws_reserve(w, 3, vb))) return rc;
+    cudaStream_t st = w->streams[0];
+    CK(cudaMemcpyAsync(w->dbuf[0], hS, mb, cudaMemcpyHostToDevice, st));
+    if (has_p) CK(cudaMemcpyAsync(w->dbuf[1], hP, mb, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(w->dbuf[2], hg, vb, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(w->dbuf[3], hl, vb, cudaMemcpyHostToDevice, st));
+    rc = solve_batched_dev<T>((const T *)w->dbuf[0], has_p ? (const T *)w->dbuf[1] : nullptr, (const T *)w->dbuf[2], (T *)w->dbuf[3],
+                              nx, N, 1, cfg, w->hd_iters, w->hd_exit, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(hl, w->dbuf[3], vb, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (iters) *iters = *(volatile uint32_t *)w->h_iters;
+    if (max_iter_exit) *max_iter_exit = *(volatile uint8_t *)w->h_exit;
+    return GBDPCG_OK;
+}
+
+// Host-resident batch: the batch is cut into chunks that alternate between two streams, so the H2D copy
+// of chunk c+1 and the D2H copy of chunk c-1 overlap the solve of chunk c (with pinned host memory;
+// pageable memory still works, the copies then serialise inside the driver).
+template <typename T>
+static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const T *hg, T *hl, uint32_t nx, uint32_t N,
+                              uint32_t batch, const gbdpcg_config *cfg, uint32_t *h_iters, uint8_t *h_exits)
+{
+    int rc = check_args(hS, hg, hl, nx, N, cfg);
+    if (rc) return rc;
+    if (batch == 0) return GBDPCG_OK;
+    gbdpcg_workspace *w;
+    rc = get_ws(user_ws, &w);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(w->mu);
+    const bool has_p = use_pinv(hP, cfg);
+    const size_t me = 3 * (size_t)N * nx * nx, ve = (size_t)N * nx;
+    if ((rc = ws_reserve(w, 0, sizeof(T) * me * batch))) return rc;
+    if (has_p && (rc = ws_reserve(w, 1, sizeof(T) * me * batch))) return rc;
+    if ((rc = ws_reserve(w, 2, sizeof(T) * ve * batch))) return rc;
+    if ((rc = ws_reserve(w, 3, sizeof(T) * ve * batch))) return rc;
+    if ((rc = ws_reserve_flags(w, batch))) return rc;
+
+    Plan p;
+    rc = make_plan<T>(nx, N, has_p, *cfg, &p);
+    if (rc) return rc;
+    if ((rc = prepare_fn(p.fn, p.cluster > 1))) return rc;
+    int resident = 1;
+    if ((rc = max_resident_problems(p, &resident))) return rc;
+    if (resident < 1) resident = 1;
+    // chunk = a whole number of resident waves, about 1/8 of the batch, at least 2 waves
+    size_t chunk = ((size_t)batch / 8 + resident - 1) / resident * resident;
+    if (chunk < 2 * (size_t)resident) chunk = 2 * (size_t)resident;
+    if (chunk > batch) chunk = batch;
+
+    T *dS = (T *)w->dbuf[0], *dP = (T *)w->dbuf[1], *dg = (T *)w->dbuf[2], *dl = (T *)w->dbuf[3];
+    int ci = 0;
+    for (size_t o = 0; o < batch; o += chunk, ci++) {
+        const size_t n = (batch - o < chunk) ? batch - o : chunk;
+        cudaStream_t st = w->streams[ci & 1];
+        CK(cudaMemcpyAsync(dS + o * me, hS + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
+        if (has_p) CK(cudaMemcpyAsync(dP + o * me, hP + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(dg + o * ve, hg + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(dl + o * ve, hl + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
+        rc = launch<T>(p, dS + o * me, has_p ? dP + o * me : nullptr, dg + o * ve, dl + o * ve, nx, N, (uint32_t)n, *cfg,
+                       w->d_iters + o, w->d_exits + o, st);
+        if (rc) return rc;
+        CK(cudaMemcpyAsync(hl + o * ve, dl + o * ve, sizeof(T) * ve * n, cudaMemcpyDeviceToHost, st));
+        if (h_iters) CK(cudaMemcpyAsync(h_iters + o, w->d_iters + o, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, st));
+        if (h_exits) CK(cudaMemcpyAsync(h_exits + o, w->d_exits + o, n, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(w->streams[0]));
+    CK(cudaStreamSynchronize(w->streams[1]));
+    return GBDPCG_OK;
+}
+
+template <typename T>
+static int plan_query(uint32_t nx, uint32_t N, int has_pinv, const gbdpcg_config *cfg, gbdpcg_plan_info *out)
+{
+    Plan p;
+    int rc = make_plan<T>(nx, N, has_pinv != 0, *cfg, &p);
+    if (rc) return rc;
+    memset(out, 0, sizeof *out);
+    out->specialised = p.generic ? 0 : 1;
+    out->cluster = p.cluster; out->threads = p.threads; out->block_rows = p.bpc; out->pinv_mode = p.pmode;
+    out->smem_bytes = p.smem;
+    snprintf(out->kernel, sizeof out->kernel, "%s", p.name);
+    out->regs = -1; out->max_resident = -1;
+    // device-dependent facts: best effort (absent on a machine without a GPU)
+    cudaFuncAttributes fa;
+    if (cudaFuncGetAttributes(&fa, p.fn) == cudaSuccess) out->regs = fa.numRegs; else cudaGetLastError();
+    int dev_count = 0;
+    if (cudaGetDeviceCount(&dev_count) == cudaSuccess && dev_count > 0) {
+        int res = 0;
+        if (prepare_fn(p.fn, p.cluster > 1) == GBDPCG_OK && max_resident_problems(p, &res) == GBDPCG_OK) out->max_resident = res;
+    } else {
+        cudaGetLastError();
+    }
+    return GBDPCG_OK;
+}
+
+}  // namespace gbdpcg
+
+// ------------------------------------------------------------------------------------------------
+// extern "C"
+// ------------------------------------------------------------------------------------------------
+using namespace gbdpcg;
+
+extern "C" {
+
+void gbdpcg_config_default(gbdpcg_config *cfg)
+{
+    if (!cfg) return;
+    cfg->exit_tol = 1e-6;   // reference include/constants.cuh:17
+    cfg->max_iter = 25;     // reference include/constants.cuh:15
+    cfg->empty_pinv = 1;    // reference include/types.cuh:33
+    cfg->flags = 0;
+    cfg->cluster = 0;
+}
+
+int gbdpcg_workspace_create(gbdpcg_workspace **ws)
+{
+    if (!ws) return fail(GBDPCG_ERR_INVALID, "ws must not be NULL");
+    auto *w = new gbdpcg_workspace();
+    int rc = ws_init(w);
+    if (rc) { ws_release(w); delete w; *ws = nullptr; return rc; }
+    *ws = w;
+    return GBDPCG_OK;
+}
+
+void gbdpcg_workspace_destroy(gbdpcg_workspace *ws)
+{
+    if (!ws) return;
+    ws_release(ws);
+    delete ws;
+}
+
+#define DEFINE_TYPED(SUF, T)                                                                                                        \
+    int gbdpcg_solve_host_##SUF(gbdpcg_workspace *ws, const T *S, const T *P, const T *g, T *l, uint32_t nx, uint32_t N,            \
+                                const gbdpcg_config *cfg, uint32_t *iters, int32_t *mie)                                            \
+    { return solve_host<T>(ws, S, P, g, l, nx, N, cfg, iters, mie); }                                                               \
+    int gbdpcg_solve_dev_##SUF(gbdpcg_workspace *, const T *S, const T *P, const T *g, T *l, uint32_t nx, uint32_t N,               \
+                               const gbdpcg_config *cfg, uint32_t *d_iters, uint8_t *d_mie, void *stream)                           \
+    { return solve_batched_dev<T>(S, P, g, l, nx, N, 1, cfg, d_iters, d_mie, stream); }                                             \
+    int gbdpcg_solve_dev_sync_##SUF(gbdpcg_workspace *ws, const T *S, const T *P, const T *g, T *l, uint32_t nx, uint32_t N,        \
+                                    const gbdpcg_config *cfg, uint32_t *iters, int32_t *mie, void *stream)                          \
+    {                                                                                                                               \
+        int rc = check_args(S, g, l, nx, N, cfg);                                                                                   \
+        return rc ? rc : solve_dev_sync<T>(ws, S, P, g, l, nx, N, cfg, iters, mie, stream);                                         \
+    }                                                                                                                               \
+    int gbdpcg_solve_batched_dev_##SUF(gbdpcg_workspace *, const T *S, const T *P, const T *g, T *l, uint32_t nx, uint32_t N,       \
+                                       uint32_t batch, const gbdpcg_config *cfg, uint32_t *d_iters, uint8_t *d_mie, void *stream)   \
+    { return solve_batched_dev<T>(S, P, g, l, nx, N, batch, cfg, d_iters, d_mie, stream); }                                         \
+    int gbdpcg_solve_batched_host_##SUF(gbdpcg_workspace *ws, const T *S, const T *P, const T *g, T *l, uint32_t nx, uint32_t N,    \
+                                        uint32_t batch, const gbdpcg_config *cfg, uint32_t *h_iters, uint8_t *h_mie)                \
+    { return solve_batched_host<T>(ws, S, P, g, l, nx, N, batch, cfg, h_iters, h_mie); }
+
+DEFINE_TYPED(f32, float)
+DEFINE_TYPED(f64, double)
+#undef DEFINE_TYPED
+
+int gbdpcg_plan_query(uint32_t nx, uint32_t N, int is_f64, int has_pinv, const gbdpcg_config *cfg, gbdpcg_plan_info *out)
+{
+    gbdpcg_config def;
+    gbdpcg_config_default(&def);
+    if (!cfg) cfg = &def;
+    if (!out) return fail(GBDPCG_ERR_INVALID, "out must not be NULL");
+    if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
+    return is_f64 ? plan_query<double>(nx, N, has_pinv, cfg, out) : plan_query<float>(nx, N, has_pinv, cfg, out);
+}
+
+void *gbdpcg_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    cudaError_t e = cudaHostAlloc(&p, bytes, cudaHostAllocDefault);
+    if (e != cudaSuccess) { fail_cuda(e, "cudaHostAlloc", __LINE__); cudaGetLastError(); return nullptr; }
+    return p;
+}
+void gbdpcg_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+int gbdpcg_version(void) { return GBDPCG_VERSION; }
+const char *gbdpcg_build_arch(void) { return "sm_100a"; }
+const char *gbdpcg_last_error(void) { return tl_error.c_str(); }
+int gbdpcg_last_cuda_error(void) { return tl_cuda_error; }
+uint64_t gbdpcg_kernel_launches(void) { return g_launches.load(); }
+
+}  // extern "C"

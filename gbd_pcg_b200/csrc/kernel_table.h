@@ -1,0 +1,29 @@
+// kernel_table.h -- registry of compiled register-row kernel variants (one translation unit per (dtype, nx)).
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+namespace gbdpcg {
+
+struct RowsVariant {
+    int nx;
+    int is_f64;
+    int clustered;   // 0: one CTA per system (__syncthreads only); 1: thread-block cluster + DSMEM
+    int pmode;       // P_NONE / P_REG / P_SMEM
+    int maxt;        // __launch_bounds__ of this instantiation = max threads per CTA
+    int nxp;         // window stride per block (elements)
+    int sb;          // staging stride per block-row (elements)
+    const void *fn;  // __global__ entry
+    const char *name;
+};
+
+// State sizes with a specialised kernel.  Keep in sync with NX_LIST in csrc/Makefile.
+#define GBDPCG_FOR_EACH_NX(X) X(2) X(4) X(6) X(8) X(10) X(12) X(14) X(16)
+
+#define GBDPCG_DECLARE_TABLE(NX)                               \
+    const RowsVariant *rows_variants_f32_##NX(int *count);     \
+    const RowsVariant *rows_variants_f64_##NX(int *count);
+GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_TABLE)
+#undef GBDPCG_DECLARE_TABLE
+
+}  // namespace gbdpcg

@@ -1,0 +1,157 @@
+/*
+ * gbdpcg.h -- C ABI of the B200-native block-tridiagonal PCG solver (libgbdpcg.so).
+ *
+ * This is the drop-in boundary for the one hot path of A2R-Lab/GBD-PCG: the solve
+ * Phi^-1 S lambda = Phi^-1 gamma.  Plain pointers and sizes only; every entry point names the
+ * reference interface it replaces (paths relative to the reference tree).  The C++ header shim
+ * (gpu_pcg.cuh / interface.cuh in this directory) forwards the reference's own templates
+ * solvePCG<T> / pcg_solve<T> onto these functions; INTEGRATION.md shows the binding.
+ *
+ * Data layout (reference include/pcg.cuh:104-110, include/utils.cuh:58-84):
+ *   S, Pinv : T[3*N*nx*nx]  block-row k at k*3*nx*nx = [left | diag | right], each block column-major;
+ *             left block of row 0 and right block of row N-1 are padding and are never read.
+ *   gamma, lambda : T[N*nx].  lambda is in/out (warm start, reference include/pcg.cuh:119,215).
+ *   batched : problem i lives at S + i*3*N*nx*nx, gamma + i*N*nx, ... (problem-major slabs).
+ *
+ * Semantics (reference include/pcg.cuh:118-212): absolute exit test |r.Phi^-1 r| < exit_tol (strict),
+ * at least one iteration, iters = it+1 on convergence at loop index it, = max_iter otherwise with
+ * max_iter_exit = 1; NaN never converges; max_iter = 0 leaves lambda untouched.  Requires N >= 2.
+ * Pinv == NULL or cfg->empty_pinv != 0 selects the identity preconditioner (the reference host
+ * overload leaves d_Pinv uninitialised, include/interface.cuh:45-46; identity is its evident intent).
+ *
+ * All functions return GBDPCG_OK (0) or a negative gbdpcg_status; none of them calls exit().
+ * There is no CPU fallback: without a usable CUDA device every solve returns GBDPCG_ERR_CUDA.
+ */
+#ifndef GBDPCG_H
+#define GBDPCG_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GBDPCG_VERSION 100 /* 0.1.0 */
+
+#if defined(__GNUC__)
+#define GBDPCG_API __attribute__((visibility("default")))
+#else
+#define GBDPCG_API
+#endif
+
+typedef enum gbdpcg_status {
+    GBDPCG_OK = 0,
+    GBDPCG_ERR_INVALID = -1,     /* null pointer, nx == 0, N < 2, bad flags                                 */
+    GBDPCG_ERR_CUDA = -2,        /* a CUDA runtime call failed; see gbdpcg_last_error() / _last_cuda_error() */
+    GBDPCG_ERR_UNSUPPORTED = -3, /* (nx, N, dtype) exceeds what any kernel variant can hold on one GPU       */
+    GBDPCG_ERR_NOMEM = -4
+} gbdpcg_status;
+
+/* POD mirror of the reference's pcg_config<T> (include/types.cuh:18-35): same meaning and defaults
+ * (include/constants.cuh:14-20).  pcg_grid / pcg_block are not carried: the reference ignores them
+ * (include/interface.cuh:132 hard-codes the launch shape). */
+typedef struct gbdpcg_config {
+    double exit_tol;     /* pcg_exit_tol, default 1e-6; compared in T                                   */
+    uint32_t max_iter;   /* pcg_max_iter, default 25                                                    */
+    int32_t empty_pinv;  /* default 1: ignore Pinv and use identity                                     */
+    uint32_t flags;      /* GBDPCG_FLAG_*; 0 = let the library choose                                   */
+    uint32_t cluster;    /* 0 = auto; otherwise force thread-block-cluster size 1,2,4,8,16 (tuning/tests) */
+} gbdpcg_config;
+
+#define GBDPCG_FLAG_FORCE_GENERIC 0x1u /* use the runtime-nx fallback kernel even if a specialised one exists */
+#define GBDPCG_FLAG_PINV_SMEM 0x2u     /* keep Phi^-1 rows in shared memory instead of registers              */
+#define GBDPCG_FLAG_PINV_REG 0x4u      /* keep Phi^-1 rows in registers (fail if they do not fit)             */
+
+GBDPCG_API void gbdpcg_config_default(gbdpcg_config *cfg);
+
+/* Opaque per-device workspace: cached device buffers, pinned staging, streams.  Replaces the 20
+ * allocator calls per solve of the reference host path (include/interface.cuh:39-53,79-86,105-108,140-141).
+ * ws == NULL in any call below selects a process-wide default workspace for the current device
+ * (internally locked; the reference is not thread-safe at all). */
+typedef struct gbdpcg_workspace gbdpcg_workspace;
+GBDPCG_API int gbdpcg_workspace_create(gbdpcg_workspace **ws);
+GBDPCG_API void gbdpcg_workspace_destroy(gbdpcg_workspace *ws);
+
+/* -- host-pointer solve: replaces solvePCG<T>(T* h_S, T* h_gamma, T* h_lambda, unsigned stateSize,
+ *    unsigned knotPoints, pcg_config<T>*)   reference include/interface.cuh:24-89 (README.md:42 pcg_solve<T>).
+ *    Blocking.  h_Pinv may be NULL.  Unlike the reference it reports the iteration count (the reference
+ *    returns 1 unconditionally, include/interface.cuh:88) and does not copy S / gamma back. */
+GBDPCG_API int gbdpcg_solve_host_f32(gbdpcg_workspace *ws, const float *h_S, const float *h_Pinv, const float *h_gamma,
+                          float *h_lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                          uint32_t *iters, int32_t *max_iter_exit);
+GBDPCG_API int gbdpcg_solve_host_f64(gbdpcg_workspace *ws, const double *h_S, const double *h_Pinv, const double *h_gamma,
+                          double *h_lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                          uint32_t *iters, int32_t *max_iter_exit);
+
+/* -- device-pointer solve: replaces solvePCG<T>(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda,
+ *    d_r, d_p, d_v_temp, d_eta_new_temp, config)   reference include/interface.cuh:92-144.
+ *    Asynchronous on `stream` (a cudaStream_t; NULL = legacy default stream).  d_iters (uint32) and
+ *    d_max_iter_exit (uint8) are device scalars and may be NULL.  The four scratch vectors of the
+ *    reference are not needed (r, p and the partial sums never leave the chip). */
+GBDPCG_API int gbdpcg_solve_dev_f32(gbdpcg_workspace *ws, const float *d_S, const float *d_Pinv, const float *d_gamma,
+                         float *d_lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                         uint32_t *d_iters, uint8_t *d_max_iter_exit, void *stream);
+GBDPCG_API int gbdpcg_solve_dev_f64(gbdpcg_workspace *ws, const double *d_S, const double *d_Pinv, const double *d_gamma,
+                         double *d_lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                         uint32_t *d_iters, uint8_t *d_max_iter_exit, void *stream);
+
+/*    Blocking form with the reference's return convention: *iters is what solvePCG returns at
+ *    include/interface.cuh:136,143; *max_iter_exit is the flag the reference computes but never reads
+ *    back (include/pcg.cuh:212, include/interface.cuh:107,141). */
+GBDPCG_API int gbdpcg_solve_dev_sync_f32(gbdpcg_workspace *ws, const float *d_S, const float *d_Pinv, const float *d_gamma,
+                              float *d_lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                              uint32_t *iters, int32_t *max_iter_exit, void *stream);
+GBDPCG_API int gbdpcg_solve_dev_sync_f64(gbdpcg_workspace *ws, const double *d_S, const double *d_Pinv, const double *d_gamma,
+                              double *d_lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                              uint32_t *iters, int32_t *max_iter_exit, void *stream);
+
+/* -- batched solves (no reference equivalent: upstream loops over single launches of pcg<>,
+ *    include/interface.cuh:132).  `batch` independent systems of identical (nx, N), problem-major slabs.
+ *    One CTA (or one thread-block cluster) per problem, persistent over the batch.
+ *    _dev: asynchronous on `stream`; d_iters[batch] (uint32) / d_max_iter_exit[batch] (uint8) may be NULL.
+ *    _host: blocking; copies are chunked and overlapped with the solves; pointers may be pageable or pinned. */
+GBDPCG_API int gbdpcg_solve_batched_dev_f32(gbdpcg_workspace *ws, const float *d_S, const float *d_Pinv, const float *d_gamma,
+                                 float *d_lambda, uint32_t nx, uint32_t N, uint32_t batch, const gbdpcg_config *cfg,
+                                 uint32_t *d_iters, uint8_t *d_max_iter_exit, void *stream);
+GBDPCG_API int gbdpcg_solve_batched_dev_f64(gbdpcg_workspace *ws, const double *d_S, const double *d_Pinv, const double *d_gamma,
+                                 double *d_lambda, uint32_t nx, uint32_t N, uint32_t batch, const gbdpcg_config *cfg,
+                                 uint32_t *d_iters, uint8_t *d_max_iter_exit, void *stream);
+GBDPCG_API int gbdpcg_solve_batched_host_f32(gbdpcg_workspace *ws, const float *h_S, const float *h_Pinv, const float *h_gamma,
+                                  float *h_lambda, uint32_t nx, uint32_t N, uint32_t batch, const gbdpcg_config *cfg,
+                                  uint32_t *h_iters, uint8_t *h_max_iter_exit);
+GBDPCG_API int gbdpcg_solve_batched_host_f64(gbdpcg_workspace *ws, const double *h_S, const double *h_Pinv, const double *h_gamma,
+                                  double *h_lambda, uint32_t nx, uint32_t N, uint32_t batch, const gbdpcg_config *cfg,
+                                  uint32_t *h_iters, uint8_t *h_max_iter_exit);
+
+/* -- launch-plan query: replaces pcgSharedMemSize<T> (reference include/pcg.cuh:13-20) and
+ *    checkPcgOccupancy<T> (include/pcg.cuh:23-49) with what THIS library would launch. */
+typedef struct gbdpcg_plan_info {
+    int32_t specialised;   /* 1: register-row kernel compiled for this nx; 0: runtime-nx fallback */
+    int32_t cluster;       /* CTAs per problem                                                   */
+    int32_t threads;       /* threads per CTA                                                    */
+    int32_t block_rows;    /* block-rows (knot points) owned by one CTA                          */
+    int32_t pinv_mode;     /* 0 identity, 1 registers, 2 shared memory, 3 global (fallback)      */
+    int32_t regs;          /* registers per thread of the chosen kernel                          */
+    uint64_t smem_bytes;   /* dynamic shared memory per CTA                                      */
+    int32_t max_resident;  /* problems resident at once on the current device                    */
+    char kernel[96];       /* variant name, for logs                                             */
+} gbdpcg_plan_info;
+GBDPCG_API int gbdpcg_plan_query(uint32_t nx, uint32_t N, int is_f64, int has_pinv, const gbdpcg_config *cfg,
+                      gbdpcg_plan_info *out);
+
+/* -- pinned host memory for callers that want full-rate copies through the _host entry points. */
+GBDPCG_API void *gbdpcg_host_alloc(size_t bytes);
+GBDPCG_API void gbdpcg_host_free(void *p);
+
+/* -- diagnostics */
+GBDPCG_API int gbdpcg_version(void);
+GBDPCG_API const char *gbdpcg_build_arch(void);       /* "sm_100a" */
+GBDPCG_API const char *gbdpcg_last_error(void);       /* thread-local message of the last failing call */
+GBDPCG_API int gbdpcg_last_cuda_error(void);          /* thread-local cudaError_t of the last failing call (0 if none) */
+GBDPCG_API uint64_t gbdpcg_kernel_launches(void);     /* number of solver kernels this process has launched */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GBDPCG_H */
