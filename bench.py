@@ -1,0 +1,433 @@
+#!/usr/bin/env python
+"""bench.py -- batched block-tridiagonal PCG solves/s on B200 (BASELINE.json metric), one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one batch: 8192 independent iiwa-sized systems
+(knot points N=32, state size nx=14, fp32, symmetric-stair Phi^-1, tol 1e-6: BASELINE config C5 = 8192 x C2)
+per GPU (weak scaling: every rank owns its own 8192 problems, no collective on the data path).
+
+  value      whole-job solves/s with inputs resident in HBM, CUDA events around each launch, max over ranks
+  e2e        same metric through the host-pointer C ABI (gbdpcg_solve_batched_host_f32): pinned host buffers,
+             H2D + solve + D2H inside the timed region
+  roofline   HBM roofline of the batched kernel (algorithmic bytes / launch time vs MEASURED_PEAKS.json)
+  single_solve   p50/p99 latency of ONE C2 solve (the north-star latency target) in three scopes
+  cpu_baseline   the host oracle (oracle/, test infrastructure) on the box's cores, bounded sample
+
+--impl reference runs the UNMODIFIED reference CUDA kernel (oracle/_ref, built from /root/reference by
+oracle/Makefile) on the same systems: it has no batch API, so its "batch" is a loop of single cooperative
+launches (include/interface.cuh:130-132), the scope most favourable to it.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NX, NU, N_KNOT, DTYPE, TOL, MAX_ITER = 14, 7, 32, np.float32, 1e-6, 1000
+PRECOND = "stair"
+BATCH = 8192
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons during the timed region (NVML; nvidia-smi fields of the recipe)."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20, "hw_thermal_slowdown": 0x40,
+                 "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10, "applications_clocks_setting": 0x2}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def start(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thr:
+            self._thr.join()
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": []}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    return rank, local, world
+
+
+def pct(xs, q):
+    xs = sorted(xs)
+    return xs[min(len(xs) - 1, int(round(q * (len(xs) - 1))))]
+
+
+def make_batch(seed0, count):
+    from gbd_pcg_b200 import synth
+    return synth.lqr_schur_batch(NX, NU, N_KNOT, range(seed0, seed0 + count), PRECOND, DTYPE)
+
+
+def pinned_array(lib, shape, dtype):
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = lib.gbdpcg_host_alloc(n)
+    if not p:
+        raise MemoryError("gbdpcg_host_alloc failed")
+    buf = (C.c_char * n).from_address(p)
+    return np.frombuffer(buf, dtype=dtype).reshape(shape), p
+
+
+# ---------------------------------------------------------------------------------------------------
+def time_single_solves(torch, launch, d_l, n_warm=100, n_timed=1000):
+    """Kernel-scope latency of one solve: CUDA events around each launch.  A ~60 us spin kernel is queued first
+    so that the host is always ahead of the device and the events bracket only the solver kernel."""
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_timed)]
+    for _ in range(n_warm):
+        d_l.zero_()
+        launch()
+    torch.cuda.synchronize()
+    for a, b in evs:
+        torch.cuda._sleep(120000)
+        d_l.zero_()
+        a.record()
+        launch()
+        b.record()
+    torch.cuda.synchronize()
+    return [a.elapsed_time(b) * 1e3 for a, b in evs]  # microseconds
+
+
+def time_blocking_calls(call, n_warm=20, n_timed=200):
+    for _ in range(n_warm):
+        call()
+    ts = []
+    for _ in range(n_timed):
+        t0 = time.perf_counter()
+        call()
+        ts.append((time.perf_counter() - t0) * 1e6)
+    return ts
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import gbd_pcg_b200 as g
+    from gbd_pcg_b200 import _lib, layout
+
+    rank, local, world = dist_env()
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    lib = _lib.lib()
+    batch = args.batch
+
+    S, P, gam = make_batch(rank * batch, batch)
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (S, P, gam))
+    d_l = torch.zeros(batch, N_KNOT * NX, dtype=torch.float32, device="cuda")
+    d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+    d_ex = torch.zeros(batch, dtype=torch.uint8, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=TOL, pcg_max_iter=MAX_ITER, empty_pinv=0)
+    plan = g.plan_query(NX, N_KNOT, DTYPE, True, cfg)
+
+    def step():
+        g.solve_batched_dev(NX, N_KNOT, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        d_l.zero_()
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = g.kernel_launches()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for a, b in evs:
+        d_l.zero_()
+        a.record()
+        step()
+        b.record()
+    barrier()
+    launches = g.kernel_launches() - launches0
+    clocks = sampler.stop()
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = float(total_ms.item()) / args.steps
+    value = batch * world / (ms_per_step * 1e-3)
+    iters = d_it.cpu().numpy()
+    assert int(d_ex.sum().item()) == 0, "some problems hit max_iter"
+
+    # ---- end to end through the host-pointer C ABI (pinned host buffers) ----
+    hS, pS = pinned_array(lib, S.shape, DTYPE); hS[:] = S
+    hP, pP = pinned_array(lib, P.shape, DTYPE); hP[:] = P
+    hg, pg = pinned_array(lib, gam.shape, DTYPE); hg[:] = gam
+    hl, pl = pinned_array(lib, gam.shape, DTYPE)
+    e2e_steps = max(2, min(args.steps, 5))
+    for _ in range(2):
+        hl[:] = 0
+        g.solve_batched_host(hS, hP, hg, hl, NX, N_KNOT, batch, cfg)
+    barrier()
+    t_e2e = 0.0
+    for _ in range(e2e_steps):
+        hl[:] = 0
+        t0 = time.perf_counter()
+        e_it, e_ex = g.solve_batched_host(hS, hP, hg, hl, NX, N_KNOT, batch, cfg)
+        t_e2e += time.perf_counter() - t0
+    e2e_t = torch.tensor([t_e2e / e2e_steps], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_value = batch * world / float(e2e_t.item())
+    assert np.array_equal(e_it, iters.astype(np.uint32)), "host path and device path disagree"
+    h2d = (S.nbytes + P.nbytes + gam.nbytes + hl.nbytes)
+    d2h = (hl.nbytes + 4 * batch + batch)
+    for p in (pS, pP, pg, pl):
+        lib.gbdpcg_host_free(p)
+
+    # ---- strong-scaling supplement: the SAME 8192 problems partitioned by problem index over the ranks ----
+    from gbd_pcg_b200.partition import slab
+    lo, hi = slab(rank, world, batch)
+    nloc = hi - lo
+
+    def step_strong():
+        g.solve_batched_dev(NX, N_KNOT, nloc, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
+
+    for _ in range(3):
+        step_strong()
+    barrier()
+    evs2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for a, b in evs2:
+        d_l.zero_()
+        a.record()
+        step_strong()
+        b.record()
+    barrier()
+    strong_ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs2)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(strong_ms, op=dist.ReduceOp.MAX)
+    strong_value = batch / (float(strong_ms.item()) / args.steps * 1e-3)
+
+    out = None
+    if rank == 0:
+        peak, peak_src = peaks()
+        bytes_per_solve = layout.algorithmic_bytes(NX, N_KNOT, 4, True)
+        launch_s = statistics.mean(step_ms) * 1e-3
+        achieved = bytes_per_solve * batch / launch_s / 1e9
+
+        # ---- single-solve latency (C2, seed 0), kernel scope / device API / host API ----
+        S1, P1, g1 = (torch.from_numpy(a[0].copy()).cuda() for a in (S, P, gam))
+        l1 = torch.zeros(N_KNOT * NX, dtype=torch.float32, device="cuda")
+        i1 = torch.zeros(1, dtype=torch.int32, device="cuda")
+        x1 = torch.zeros(1, dtype=torch.uint8, device="cuda")
+        lat_k = time_single_solves(torch, lambda: g.solve_dev_async(NX, N_KNOT, S1, P1, g1, l1, cfg, i1, x1), l1)
+        it1 = int(i1.item())
+
+        def dev_call():
+            l1.zero_()
+            g.api._solve_dev(NX, N_KNOT, S1, P1, g1, l1, config=cfg)
+        lat_d = time_blocking_calls(dev_call)
+        hS1, hP1, hg1 = S[0].copy(), P[0].copy(), gam[0].copy()
+        hl1 = np.zeros(N_KNOT * NX, dtype=DTYPE)
+
+        def host_call():
+            hl1[:] = 0
+            g.pcg_solve(hS1, hg1, hl1, NX, N_KNOT, cfg, h_Pinv=hP1)
+        lat_h = time_blocking_calls(host_call)
+
+        # ---- CPU baseline: host oracle on a bounded sample, all cores ----
+        from oracle import oracle
+        cores = os.cpu_count() or 1
+        ns = min(batch, 8192)
+        lam_c = np.zeros((ns, N_KNOT * NX), dtype=DTYPE)
+        t0 = time.perf_counter()
+        _, it_c, _ = oracle.pcg_batched(S[:ns], P[:ns], gam[:ns], lam_c, NX, N_KNOT, TOL, MAX_ITER, order=0, threads=cores)
+        t_cpu = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        for i in range(50):
+            oracle.pcg(S[i], P[i], gam[i], lam_c[0] * 0, NX, N_KNOT, TOL, MAX_ITER)
+        t_cpu1 = (time.perf_counter() - t0) / 50
+
+        out = {
+            "metric": "batched PCG solves/s (8192 x N=32,nx=14 fp32 per GPU)", "value": value, "unit": "solves/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C5: 8192 independent iiwa MPC systems per GPU (knot points 32, state size 14, fp32, "
+                                   "symmetric-stair preconditioner, tol 1e-6), seeds rank*8192+i",
+                       "batch_per_gpu": batch, "nx": NX, "knot_points": N_KNOT, "precond": PRECOND, "exit_tol": TOL,
+                       "l2": "inputs (1.25 GB/GPU) larger than L2; no flush needed", "kernel": plan["kernel"],
+                       "threads": plan["threads"], "cluster": plan["cluster"], "smem_bytes": plan["smem_bytes"]},
+            "pcg_iters": {"min": int(iters.min()), "mean": float(iters.mean()), "max": int(iters.max())},
+            "iterations_per_s": float(iters.mean()) * value,
+            "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "steps": e2e_steps, "api": "gbdpcg_solve_batched_host_f32 (pinned host buffers, chunked 2-stream overlap)"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src, "bytes_per_solve": bytes_per_solve,
+                         "kernel_ms": launch_s * 1e3},
+            "clocks": clocks,
+            "strong_scaling": {"value": strong_value, "unit": "solves/s", "total_batch": batch,
+                               "note": "the same 8192 problems partitioned by problem index over the ranks"},
+            "single_solve": {"config": "C2 N=32 nx=14 fp32 stair, seed 0", "iters": it1,
+                             "kernel_p50_us": pct(lat_k, 0.5), "kernel_p99_us": pct(lat_k, 0.99),
+                             "iterations_per_s": it1 / (pct(lat_k, 0.5) * 1e-6),
+                             "dev_api_p50_us": pct(lat_d, 0.5), "dev_api_p99_us": pct(lat_d, 0.99),
+                             "host_api_p50_us": pct(lat_h, 0.5), "host_api_p99_us": pct(lat_h, 0.99)},
+            "cpu_baseline": {"value": ns / t_cpu, "unit": "solves/s", "cores": cores, "kind": "port",
+                             "sample": f"{ns} of the {batch} systems, host oracle (oracle/pcg_oracle.c), {cores} threads",
+                             "single_thread_solve_us": t_cpu1 * 1e6, "iters_mean": float(it_c.mean())},
+        }
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def run_reference(args):
+    """Reference arm: the unmodified reference CUDA kernel, one cooperative launch per system."""
+    rank, local, world = dist_env()
+    if rank != 0:
+        return None
+    import torch
+
+    from oracle import oracle, ref_cuda
+    torch.cuda.set_device(0)
+    if not ref_cuda.has(DTYPE, NX, N_KNOT):
+        return {"impl": "reference", "unavailable": "oracle/_ref/libref_pcg_f32_14_32.so not built (needs /root/reference at build time)"}
+    ref = ref_cuda.get(DTYPE, NX, N_KNOT)
+    sample = min(args.batch, args.ref_sample)
+    S, P, gam = make_batch(0, sample)
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (S, P, gam))
+    d_l = torch.zeros(sample, N_KNOT * NX, dtype=torch.float32, device="cuda")
+
+    # pre-sliced views keep Python overhead off the device's critical path
+    rows = [(d_S[i], d_P[i], d_g[i], d_l[i]) for i in range(sample)]
+
+    def step():
+        for s, p, gg, l in rows:
+            ref.launch(s, p, gg, l, MAX_ITER, TOL)
+
+    for _ in range(max(args.warmup, 3)):
+        d_l.zero_()
+        step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for a, b in evs:
+        d_l.zero_()
+        a.record()
+        step()
+        b.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    ms_per_step = statistics.mean(step_ms)
+    value = sample / (ms_per_step * 1e-3)
+
+    # single-solve latency, same three scopes as our arm
+    l1 = d_l[0]
+    lat_k = time_single_solves(torch, lambda: ref.launch(d_S[0], d_P[0], d_g[0], l1, MAX_ITER, TOL), l1)
+    it1 = int(ref.d_iters.item())
+
+    def dev_call():
+        l1.zero_()
+        ref.solve_dev_api(d_S[0], d_P[0], d_g[0], l1, MAX_ITER, TOL)
+    lat_d = time_blocking_calls(dev_call)
+    hS1, hg1, hl1 = S[0].copy(), gam[0].copy(), np.zeros(N_KNOT * NX, dtype=DTYPE)
+
+    def host_call():  # time only: the reference never initialises d_Pinv on this path (interface.cuh:45-46)
+        hl1[:] = 0
+        ref.solve_host_api(hS1, hg1, hl1, 25, TOL)
+    lat_h = time_blocking_calls(host_call, n_warm=5, n_timed=50)
+
+    cores = os.cpu_count() or 1
+    ns = min(sample, 2048)
+    lam_c = np.zeros((ns, N_KNOT * NX), dtype=DTYPE)
+    t0 = time.perf_counter()
+    oracle.pcg_batched(S[:ns], P[:ns], gam[:ns], lam_c, NX, N_KNOT, TOL, MAX_ITER, order=1, threads=cores)
+    t_cpu = time.perf_counter() - t0
+    return {
+        "impl": "reference",
+        "metric": "batched PCG solves/s (8192 x N=32,nx=14 fp32 per GPU)", "value": value, "unit": "solves/s",
+        "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"C5 sample: {sample} of the 8192 iiwa MPC systems (knot points 32, state size 14, fp32, "
+                               "symmetric-stair preconditioner, tol 1e-6), one cooperative launch of the reference "
+                               "pcg<float,14,32> per system, back to back on one stream (it has no batch API)",
+                   "batch_per_gpu": sample, "nx": NX, "knot_points": N_KNOT, "precond": PRECOND, "exit_tol": TOL},
+        "e2e": {"value": value, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": sample * args.steps,
+        "clocks": clocks,
+        "single_solve": {"config": "C2 N=32 nx=14 fp32 stair, seed 0", "iters": it1,
+                         "kernel_p50_us": pct(lat_k, 0.5), "kernel_p99_us": pct(lat_k, 0.99),
+                         "iterations_per_s": it1 / (pct(lat_k, 0.5) * 1e-6),
+                         "dev_api_p50_us": pct(lat_d, 0.5), "dev_api_p99_us": pct(lat_d, 0.99),
+                         "host_api_p50_us_time_only_25_iters": pct(lat_h, 0.5), **ref.attrs()},
+        "cpu_baseline": {"value": ns / t_cpu, "unit": "solves/s", "cores": cores, "kind": "reference",
+                         "sample": f"reference CUDA kernel on the B200 is the line's value; this entry is the host oracle in "
+                                   f"reference reduction order on {ns} systems, {cores} threads"},
+    }
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH, help="systems per GPU")
+    ap.add_argument("--ref-sample", type=int, default=512, help="systems per step of the reference arm")
+    args = ap.parse_args()
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()
