@@ -125,10 +125,17 @@ __device__ __forceinline__ T tree_sum_smem(const T *buf)
         if constexpr (V == 4) { v[4 * i] = q.x; v[4 * i + 1] = q.y; v[4 * i + 2] = q.z; v[4 * i + 3] = q.w; }
         else                  { v[2 * i] = q.x; v[2 * i + 1] = q.y; }
     }
+    // pairwise tree for any CNT (not only powers of two): fold the upper half onto the lower half
+    int n = CNT;
 #pragma unroll
-    for (int s = CNT / 2; s >= 1; s >>= 1) {
+    for (int step = 0; step < 6; step++) {
+        if (n > 1) {
+            const int half = (n + 1) / 2;
 #pragma unroll
-        for (int i = 0; i < s; i++) v[i] += v[i + s];
+            for (int i = 0; i < CNT / 2; i++)
+                if (i + half < n) v[i] += v[i + half];
+            n = half;
+        }
     }
     return v[0];
 }

@@ -1,0 +1,159 @@
+"""CPU tests: the host oracle (oracle/pcg_oracle.c) against the derived C1 known answers, against an
+independent dense-numpy statement of the recurrence, and against dense linear algebra.  No GPU needed."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, LAMBDA_TOL, rel_err
+from gbd_pcg_b200 import layout, synth
+from helpers import PRECONDS, make_system
+from oracle import oracle
+
+KAT = json.load(open(os.path.join(GOLDEN, "c1_kat.json")))
+
+
+def test_kat_inputs_are_the_reference_example():
+    """tests/golden/c1_kat.json and synth.EXAMPLE_* both restate reference examples/pcg_solve.cu:14-25."""
+    assert np.array_equal(np.asarray(KAT["S"]), synth.EXAMPLE_S)
+    assert np.array_equal(np.asarray(KAT["gamma"]), synth.EXAMPLE_GAMMA)
+    A = layout.unpack_dense(synth.EXAMPLE_S, 2, 3)
+    assert np.allclose(A, A.T) and np.linalg.eigvalsh(A).max() < 0       # symmetric negative definite
+    assert np.allclose(np.linalg.eigvalsh(A), KAT["eigenvalues"])
+
+
+@pytest.mark.parametrize("case", [c for c in KAT["cases"] if c["dtype"] == "float64" and c["precond"] != "zero"],
+                         ids=lambda c: c["precond"])
+@pytest.mark.parametrize("order", [0, 1])
+def test_c1_fp64_known_answers(case, order):
+    S, P, g = synth.example_system(np.float64, case["precond"])
+    lam, it, ex, tr = oracle.pcg(S, None if case["precond"] == "identity" else P, g, np.zeros(6), 2, 3, 1e-6, 25, order=order, trace=True)
+    assert it == case["iters"] and ex == case["max_iter_exit"]
+    assert rel_err(lam, KAT["lambda_star"]) < 1e-9
+    # eta sequence (all but the last, which is rounding noise ~1e-21) to 1e-8
+    assert np.allclose(tr[:-1], case["eta"][:-1], rtol=1e-8)
+
+
+@pytest.mark.parametrize("case", [c for c in KAT["cases"] if c["dtype"] == "float32"], ids=lambda c: c["precond"])
+def test_c1_fp32_solution(case):
+    """fp32 iteration counts on C1 are reduction-order sensitive (cond 1.6e3): judge the solution."""
+    S, P, g = synth.example_system(np.float32, case["precond"])
+    lam, it, ex = oracle.pcg(S, None if case["precond"] == "identity" else P, g, np.zeros(6, np.float32), 2, 3, 1e-6, 25)
+    assert not ex and abs(it - case["iters"]) <= 2
+    assert rel_err(lam, KAT["lambda_star"]) < 2e-4
+
+
+def test_zero_pinv_reproduces_reference_defect_d1():
+    """All-zero Phi^-1 (what the reference host overload computes with on fresh memory, interface.cuh:45-46):
+    eta = 0 -> alpha = NaN -> never converges, 25 iterations, NaN lambda."""
+    S, _, g = synth.example_system(np.float64)
+    lam, it, ex = oracle.pcg(S, np.zeros_like(S), g, np.zeros(6), 2, 3, 1e-6, 25)
+    assert it == 25 and ex and np.isnan(lam).all()
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("nx,N", [(2, 2), (2, 3), (3, 5), (4, 8), (7, 9), (14, 32), (12, 40)])
+def test_block_row_matvec_matches_dense(nx, N, dtype):
+    rng = np.random.default_rng(nx * 100 + N)
+    M = rng.standard_normal(layout.mat_elems(nx, N)).astype(dtype)
+    M[:nx * nx] = np.nan          # padding blocks must never be read (pcg.cuh:105-106, utils.cuh:58-84)
+    M[-nx * nx:] = np.nan
+    x = rng.standard_normal(nx * N).astype(dtype)
+    y = oracle.bdmv(M, x, nx, N)
+    Md = M.copy(); Md[:nx * nx] = 0; Md[-nx * nx:] = 0
+    yd = layout.unpack_dense(Md.astype(np.float64), nx, N) @ x.astype(np.float64)
+    assert rel_err(y, yd) < (1e-5 if dtype == np.float32 else 1e-13)
+
+
+@pytest.mark.parametrize("name", ["C2", "C3", "C4"])
+@pytest.mark.parametrize("precond", PRECONDS)
+def test_oracle_vs_dense_numpy_recurrence(name, precond):
+    """Two independent statements of SURVEY App. A.1 (C block-row code vs dense numpy) agree at the parity bar."""
+    if name == "C4" and precond != "stair":
+        pytest.skip("dense 6144^2 recurrence is slow; one preconditioner is enough")
+    S, P, g, nx, N, tol, max_iter = make_system(name, precond)
+    lam0 = np.zeros(N * nx, dtype=S.dtype)
+    lam, it, ex = oracle.pcg(S, P, g, lam0, nx, N, tol, max_iter)
+    lam_n, it_n, ex_n = oracle.pcg_numpy(S, P, g, lam0, nx, N, tol, max_iter)
+    assert not ex and not ex_n and abs(it - it_n) <= 1
+    if it == it_n:
+        assert rel_err(lam, lam_n) <= LAMBDA_TOL[S.dtype]
+
+
+@pytest.mark.parametrize("name,expect", [("C2", (103, 50, 25)), ("C3", (156, 76, 38)), ("C4", (119, 60, 30))])
+def test_iteration_counts_of_the_synthetic_configs(name, expect):
+    """SURVEY App. F measured behaviour (numpy emulation): iterations for identity / block-Jacobi / stair."""
+    for pc, want in zip(PRECONDS, expect):
+        S, P, g, nx, N, tol, max_iter = make_system(name, pc)
+        _, it, ex = oracle.pcg(S, P, g, np.zeros(N * nx, dtype=S.dtype), nx, N, tol, max_iter)
+        assert not ex and abs(it - want) <= 1, (name, pc, it, want)
+
+
+@pytest.mark.parametrize("name", ["C2", "C3"])
+def test_solution_solves_the_system(name):
+    S, P, g, nx, N, tol, max_iter = make_system(name, "stair")
+    lam, it, ex = oracle.pcg(S, P, g, np.zeros(N * nx, dtype=S.dtype), nx, N, tol, max_iter)
+    x = np.linalg.solve(layout.unpack_dense(S.astype(np.float64), nx, N), g.astype(np.float64))
+    assert rel_err(lam, x) < (2e-4 if S.dtype == np.float32 else 1e-5)   # tol is on r.Pinv r, not on the error
+
+
+def test_reference_reduction_order_mode():
+    """order=1 restates GLASS's tree (reduce.cuh:35-62): same answer as plain summation to rounding, not bit-equal."""
+    S, P, g, nx, N, tol, max_iter = make_system("C2", "stair")
+    lam0 = np.zeros(N * nx, dtype=np.float32)
+    a, ia, _ = oracle.pcg(S, P, g, lam0, nx, N, tol, max_iter, order=0)
+    b, ib, _ = oracle.pcg(S, P, g, lam0, nx, N, tol, max_iter, order=1)
+    assert abs(ia - ib) <= 1
+    if ia == ib:
+        assert rel_err(a, b) < 1e-5
+    # the tree itself, on a case small enough to do by hand: n=7 -> s=3, x0+=x3,x1+=x4,x2+=x5, x0+=x6, then x0+=x1+x2
+    S2 = layout.identity_compressed(7, 2, np.float64)
+    r = np.arange(1.0, 15.0)
+    _, _, _, tr = oracle.pcg(S2, None, r, np.zeros(14), 7, 2, 0.0, 1, order=1, trace=True)
+    assert tr[0] == float((r * r).sum())
+
+
+def test_exit_semantics():
+    S, P, g, nx, N, tol, max_iter = make_system("C2", "stair")
+    lam0 = np.linspace(-1, 1, N * nx).astype(np.float32)
+    lam, it, ex = oracle.pcg(S, P, g, lam0, nx, N, tol, 0)
+    assert it == 0 and ex and np.array_equal(lam, lam0)                 # max_iter = 0: untouched
+    lam, it, ex = oracle.pcg(S, P, g, lam0 * 0, nx, N, tol, 7)
+    assert it == 7 and ex                                                # cap reached
+    g2 = g.copy(); g2[3] = np.nan
+    lam, it, ex = oracle.pcg(S, P, g2, lam0 * 0, nx, N, tol, 9)
+    assert it == 9 and ex and np.isnan(lam).any()                        # NaN never satisfies |eta| < tol
+    lam, it, ex = oracle.pcg(S, P, g, lam0 * 0, nx, N, 1e30, 50)
+    assert it == 1 and not ex                                            # at least one iteration always runs
+    with pytest.raises(ValueError):
+        oracle.pcg(S, P, g, lam0, nx, 1, tol, 5)                         # N >= 2 (utils.cuh:21-25)
+
+
+def test_warm_start_takes_fewer_iterations():
+    S, P, g, nx, N, tol, max_iter = make_system("C2", "stair")
+    cold, it_cold, _ = oracle.pcg(S, P, g, np.zeros(N * nx, np.float32), nx, N, tol, max_iter)
+    warm, it_warm, _ = oracle.pcg(S, P, g, cold * np.float32(1.001), nx, N, tol, max_iter)
+    assert it_warm < it_cold and rel_err(warm, cold) < 1e-4
+
+
+def test_batched_driver_equals_single():
+    nx, nu, N = 6, 3, 10
+    S, P, g = synth.lqr_schur_batch(nx, nu, N, range(9), "stair", np.float64)
+    lam, its, exs = oracle.pcg_batched(S, P, g, np.zeros_like(g), nx, N, 1e-10, 500, threads=3)
+    for i in range(9):
+        l1, i1, e1 = oracle.pcg(S[i], P[i], g[i], np.zeros(N * nx), nx, N, 1e-10, 500)
+        assert its[i] == i1 and exs[i] == e1 and np.array_equal(lam[i], l1)
+
+
+def test_generator_matches_survey_recipe():
+    """C2 is negative definite with cond ~ 456 and eigenvalues in [-6.99, -0.0153]."""
+    S, P, g = synth.lqr_schur(14, 7, 32, 0, "stair", np.float64)
+    A = layout.unpack_dense(S, 14, 32)
+    ev = np.linalg.eigvalsh(A)
+    assert np.allclose(A, A.T) and ev.max() < 0
+    assert 400 < ev.min() / ev.max() < 500
+    Pd = layout.unpack_dense(P, 14, 32)
+    assert np.allclose(Pd, Pd.T)
+    # stair preconditioner: diagonal blocks are the inverses of S's diagonal blocks
+    assert np.allclose(Pd[:14, :14] @ A[:14, :14], np.eye(14), atol=1e-10)
