@@ -13,6 +13,7 @@
 
 #include "gbdpcg.h"
 #include "kernel_table.h"
+#include "pcg_fused.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
 
@@ -53,6 +54,8 @@ static constexpr size_t kMaxDynSmem = 227 * 1024;  // sm_100: 227 KB opt-in dyna
 
 struct Plan {
     bool generic = false;
+    bool fused_kernel = false;        // second-generation kernel (pcg_fused.cuh)
+    int rpt = 1, fused = 0;           // rows per thread, single-reduction recurrence
     const RowsVariant *v = nullptr;
     int cluster = 1, bpc = 0, threads = 0, nbuf = 1, pmode = P_NONE;
     size_t smem = 0;
@@ -73,6 +76,60 @@ static void all_variants(bool f64, int nx, const RowsVariant **tab, int *cnt)
     }
 }
 
+static void fused_variants(bool f64, int nx, int fused, const FusedVariant **tab, int *cnt)
+{
+    *tab = nullptr;
+    *cnt = 0;
+    switch (nx) {
+#define CASE(NX)                                                                                                       \
+    case NX:                                                                                                           \
+        *tab = f64 ? (fused ? fused_variants_f64_##NX##_1(cnt) : fused_variants_f64_##NX##_0(cnt))                     \
+                   : (fused ? fused_variants_f32_##NX##_1(cnt) : fused_variants_f32_##NX##_0(cnt));                    \
+        break;
+        GBDPCG_FOR_EACH_NX(CASE)
+#undef CASE
+        default: break;
+    }
+}
+
+// Second-generation kernel: smallest cluster that fits, Phi^-1 in registers when possible.
+template <typename T>
+static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+{
+    constexpr bool f64 = sizeof(T) == 8;
+    int fused = f64 ? 0 : 1;                                   // default recurrence per dtype
+    if (cfg.flags & GBDPCG_FLAG_TEXTBOOK) fused = 0;
+    if (cfg.flags & GBDPCG_FLAG_FUSED) fused = 1;
+    const FusedVariant *tab;
+    int cnt;
+    fused_variants(f64, (int)nx, fused, &tab, &cnt);
+    if (cnt == 0) return false;
+    static const int cl_opts[] = {1, 2, 4, 8, 16};
+    for (int cl : cl_opts) {
+        if (cfg.cluster && (int)cfg.cluster != cl) continue;
+        const int bpc = ((int)N + cl - 1) / cl;
+        int pm_opts[2] = {P_REG, P_SMEM};
+        int n_pm = 2;
+        if (!has_p) { pm_opts[0] = P_NONE; n_pm = 1; }
+        else if (cfg.flags & GBDPCG_FLAG_PINV_SMEM) { pm_opts[0] = P_SMEM; n_pm = 1; }
+        else if (cfg.flags & GBDPCG_FLAG_PINV_REG) { n_pm = 1; }
+        for (int ip = 0; ip < n_pm; ip++) {
+            for (int i = 0; i < cnt; i++) {
+                const FusedVariant *v = &tab[i];
+                const int threads = round_up(bpc * ((int)nx / v->rpt), 32);
+                if (v->clustered != (cl > 1) || v->pmode != pm_opts[ip] || threads > v->maxt) continue;
+                const size_t smem = make_fused_plan<T>((int)nx, v->nxp, bpc, v->pmode, v->pmode == P_REG ? 2 : 1).total;
+                if (smem > kMaxDynSmem) continue;
+                out->generic = false; out->fused_kernel = true; out->v = nullptr; out->cluster = cl; out->bpc = bpc;
+                out->threads = threads; out->nbuf = (v->pmode == P_REG) ? 2 : 1; out->pmode = v->pmode; out->smem = smem;
+                out->fn = v->fn; out->name = v->name; out->rpt = v->rpt; out->fused = v->fused;
+                return true;
+            }
+        }
+    }
+    return false;
+}
+
 template <typename T>
 static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
 {
@@ -86,6 +143,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     const RowsVariant *tab;
     int cnt;
     all_variants(f64, (int)nx, &tab, &cnt);
+    if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK;
     if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
         static const int cl_opts[] = {1, 2, 4, 8, 16};
         for (int cl : cl_opts) {
@@ -204,6 +262,11 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
     a.S = S; a.Pinv = P; a.gamma = gamma; a.lambda = lambda; a.iters = d_iters; a.exits = d_exits;
     a.mat_stride = 3ull * N * nx * nx; a.vec_stride = (unsigned long long)N * nx;
     a.N = N; a.batch = batch; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg.max_iter; a.two_buffers = (p.nbuf == 2);
+    if (p.fused_kernel) {
+        // field reused as the TMA switch: bulk copies need 16-byte aligned sources (strides are multiples of 16 for even nx)
+        const bool aligned = ((uintptr_t)S % 16 == 0) && (!P || (uintptr_t)P % 16 == 0) && ((a.mat_stride * sizeof(T)) % 16 == 0);
+        a.two_buffers = (aligned && p.pmode != P_SMEM && !(cfg.flags & GBDPCG_FLAG_NO_TMA)) ? 1u : 0u;
+    }
     a.tol = (T)cfg.exit_tol;
 
     cudaLaunchConfig_t lc = {};

@@ -26,4 +26,25 @@ struct RowsVariant {
 GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_TABLE)
 #undef GBDPCG_DECLARE_TABLE
 
+// Fused kernel (pcg_fused.cuh): one table per (dtype, nx, recurrence).
+struct FusedVariant {
+    int nx;
+    int is_f64;
+    int rpt;         // rows per thread
+    int clustered;
+    int pmode;
+    int fused;       // 1: single-reduction (Chronopoulos-Gear) order, 0: the reference's two-reduction order
+    int maxt;
+    int nxp;
+    const void *fn;
+    const char *name;
+};
+#define GBDPCG_DECLARE_FUSED(NX)                                   \
+    const FusedVariant *fused_variants_f32_##NX##_0(int *count);   \
+    const FusedVariant *fused_variants_f32_##NX##_1(int *count);   \
+    const FusedVariant *fused_variants_f64_##NX##_0(int *count);   \
+    const FusedVariant *fused_variants_f64_##NX##_1(int *count);
+GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_FUSED)
+#undef GBDPCG_DECLARE_FUSED
+
 }  // namespace gbdpcg

@@ -1,0 +1,644 @@
+// pcg_fused.cuh -- the sm_100a PCG kernel (second generation of this library's hot path).
+//
+// One thread-block cluster (1..16 CTAs) owns one system for the whole solve and is persistent over a
+// batch of systems.  A thread owns R rows (R = 2 for fp32, 1 for fp64) of the (N*nx)-dimensional system
+// and keeps those rows of S and Phi^-1 in REGISTERS; lambda, r, p, ... live in registers too.  The only
+// data that moves per iteration is the vector being multiplied: it is published into a small shared
+// "window" (own block-rows + one halo block on each side; the halo of the neighbouring CTA is written
+// through DSMEM) and read back with 16-byte broadcast loads.
+//
+// What the reference does per iteration (include/pcg.cuh:154-208): 2 block-row mat-vecs through shared
+// memory with nx of 64 threads working, 2 grid-wide dot products (global partials + grid.sync +
+// redundant re-reduction), 4 grid.sync.  What this kernel does per iteration:
+//   FUSED = true  (default for fp32): Chronopoulos-Gear form of the same recurrence -- r~ = Phi^-1 r and
+//       w = S r~ are formed first, then gamma = r.r~ and delta = w.r~ are reduced TOGETHER, and
+//       beta = gamma/gamma_old, alpha = gamma/(delta - beta*gamma/alpha_old), p = r~ + beta p,
+//       s = w + beta s (= S p), lambda += alpha p, r -= alpha s.  Same iterates in exact arithmetic, same
+//       exit test on the same quantity (|r.Phi^-1 r| < tol after each update), ONE reduction and three
+//       block barriers per iteration.
+//   FUSED = false (default for fp64, or GBDPCG_FLAG_TEXTBOOK): the reference's own order of operations
+//       (two reductions, four barriers).
+// Reductions are warp shuffles + one shared-memory hop (+ one DSMEM hop per CTA in cluster mode); every
+// thread re-sums the same partials in the same order, so alpha, beta and the exit decision are
+// bit-identical in every thread of every CTA (the reference gets this from re-reducing d_eta_new_temp in
+// every block, include/pcg.cuh:189-195).  There is no grid.sync and no global-memory traffic inside the loop.
+//
+// Batched mode: while a system is being solved, the NEXT system's S and Phi^-1 block-rows are prefetched
+// into shared memory by the TMA engine (cp.async.bulk + mbarrier), so HBM latency is hidden behind the
+// iterations and every matrix byte is read from HBM exactly once.
+//
+// Algorithm restated from reference include/pcg.cuh:118-212.
+#pragma once
+#include <cooperative_groups.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "pcg_rows.cuh"  // KernelArgs, Geo, Vec16, abs_t, warp helpers, stage_block_rows, P_* enums
+
+#ifndef FUSED_NCH_R2
+#define FUSED_NCH_R2 2
+#endif
+#ifndef FUSED_LOAD64
+#define FUSED_LOAD64 1
+#endif
+#ifndef FUSED_QBUF
+#define FUSED_QBUF 2
+#endif
+
+namespace gbdpcg {
+
+// ---------------------------------------------------------------------------------------------
+// shared-memory plan (host sizes it, device carves it)
+// ---------------------------------------------------------------------------------------------
+struct FusedPlan {
+    uint32_t mbar_off, red_off, cred_off, winA_off, winB_off, stage_off, psm_off, total;
+};
+// nstage: number of matrices the staging area holds side by side (2: S and Phi^-1 for P_REG; else 1)
+// PMODE == P_SMEM keeps Phi^-1 resident in its own area (psm) for the whole solve.
+template <typename T>
+__host__ __device__ inline FusedPlan make_fused_plan(int nx, int nxp, int bpc, int pmode, int nstage)
+{
+    FusedPlan p;
+    uint32_t o = 0;
+    p.mbar_off = o;  o += 16;
+    p.red_off = o;   o += 2 * 2 * 32 * (uint32_t)sizeof(T);       // 2 slots x [warp][2] partials, up to 32 warps
+    p.cred_off = o;  o += 2 * 2 * 16 * (uint32_t)sizeof(T);       // 2 slots x [cta][2] partials, up to 16 CTAs
+    p.winA_off = o;  o += (uint32_t)round_up((bpc + 2) * nxp * (int)sizeof(T), 16);
+    p.winB_off = o;  o += (uint32_t)round_up((bpc + 2) * nxp * (int)sizeof(T), 16);
+    const uint32_t mat = (uint32_t)round_up(bpc * 3 * nx * nx * (int)sizeof(T), 16);
+    p.psm_off = o;   o += (pmode == P_SMEM) ? mat : 0;
+    p.stage_off = o; o += (uint32_t)nstage * mat;
+    p.total = o;
+    return p;
+}
+
+// ---------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + bulk async copy (TMA engine, 1-D)
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t mbar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t mbar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(mbar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(mbar)
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+// Cooperative global -> shared copy of `count` contiguous elements (the unpadded image of this CTA's block-rows).
+// Used when the TMA path is not available (source not 16-byte aligned, or Phi^-1 resident in shared memory).
+template <typename T>
+__device__ __noinline__ void stage_image(const T *__restrict__ src, T *__restrict__ dst, int count)
+{
+    constexpr int U = 8;
+    const int nthr = blockDim.x, t = threadIdx.x;
+    if (count <= 0) return;
+    if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (count * (int)sizeof(T)) % 16 == 0) {
+        const int total = count * (int)sizeof(T) / 16;
+        const uint4 *s4 = reinterpret_cast<const uint4 *>(src);
+        uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+        for (int base = 0; base < total; base += U * nthr) {
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < total) v[u] = __ldg(s4 + q); }
+#pragma unroll
+            for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < total) d4[q] = v[u]; }
+        }
+    } else {
+        for (int base = 0; base < count; base += U * nthr) {
+            T v[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < count) v[u] = __ldg(src + q); }
+#pragma unroll
+            for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < count) dst[q] = v[u]; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// packed arithmetic: a "pair" is two T values that are reduced / updated together
+// ---------------------------------------------------------------------------------------------
+template <typename T> struct Pair;
+template <> struct Pair<float> {
+    float2 v;
+    __device__ __forceinline__ Pair() {}
+    __device__ __forceinline__ Pair(float a, float b) : v(make_float2(a, b)) {}
+    __device__ __forceinline__ float x() const { return v.x; }
+    __device__ __forceinline__ float y() const { return v.y; }
+    __device__ __forceinline__ Pair operator+(const Pair &o) const { Pair r; r.v = __fadd2_rn(v, o.v); return r; }
+};
+template <> struct Pair<double> {
+    double a, b;
+    __device__ __forceinline__ Pair() {}
+    __device__ __forceinline__ Pair(double a_, double b_) : a(a_), b(b_) {}
+    __device__ __forceinline__ double x() const { return a; }
+    __device__ __forceinline__ double y() const { return b; }
+    __device__ __forceinline__ Pair operator+(const Pair &o) const { return Pair(a + o.a, b + o.b); }
+};
+template <typename T>
+__device__ __forceinline__ Pair<T> shfl_xor_pair(const Pair<T> &p, int m)
+{
+    return Pair<T>(__shfl_xor_sync(0xffffffffu, p.x(), m), __shfl_xor_sync(0xffffffffu, p.y(), m));
+}
+
+// Sum of CNT (value0, value1) pairs stored interleaved in shared memory; fixed pairwise order, identical
+// in every thread.  CNT is a multiple of 2 (fp32: one 16-byte load = 2 pairs) or any (fp64: 1 pair per load).
+template <typename T, int CNT>
+__device__ __forceinline__ Pair<T> pair_tree_sum(const T *buf)
+{
+    Pair<T> v[CNT];
+    if constexpr (sizeof(T) == 4) {
+        static_assert(CNT % 2 == 0, "");
+#pragma unroll
+        for (int i = 0; i < CNT / 2; i++) {
+            const float4 q = reinterpret_cast<const float4 *>(buf)[i];
+            v[2 * i] = Pair<T>(q.x, q.y);
+            v[2 * i + 1] = Pair<T>(q.z, q.w);
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < CNT; i++) {
+            const double2 q = reinterpret_cast<const double2 *>(buf)[i];
+            v[i] = Pair<T>(q.x, q.y);
+        }
+    }
+    int n = CNT;
+#pragma unroll
+    for (int step = 0; step < 6; step++) {
+        if (n > 1) {
+            const int half = (n + 1) / 2;
+#pragma unroll
+            for (int i = 0; i < CNT / 2; i++)
+                if (i + half < n) v[i] = v[i] + v[i + half];
+            n = half;
+        }
+    }
+    return v[0];
+}
+
+// ---------------------------------------------------------------------------------------------
+// block-row mat-vec for the R rows a thread owns:  y[row] = sum_k M[row][k] * w[j(k)*NXP + c(k)],  k = j*NX + c
+// `w` points at the window slot of block b-1.  M comes from registers, or (SMEM_M) from shared memory
+// where element (row, k) sits at Ms[k*NX + row] (the global column-major image of the block-row).
+// ---------------------------------------------------------------------------------------------
+template <typename T, int NX, int R, bool SMEM_M>
+__device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *__restrict__ Ms, const T *__restrict__ w, T (&y)[R])
+{
+    constexpr int NXP = Geo<T>::nxp(NX);
+    auto m = [&](int row, int k) -> T {
+        if constexpr (SMEM_M) return Ms[k * NX + row];
+        else return M[row][k];
+    };
+    if constexpr (sizeof(T) == 4 && NX % 2 == 0) {
+        constexpr int NCH = (R == 1) ? 4 : FUSED_NCH_R2;  // independent FFMA2 chains per row
+        constexpr int NQ = (NX + 3) / 4;       // 16-byte loads per window block
+        float2 acc[R][NCH];
+#pragma unroll
+        for (int row = 0; row < R; row++)
+#pragma unroll
+            for (int ch = 0; ch < NCH; ch++) acc[row][ch] = make_float2(0.f, 0.f);
+        // Software pipeline over the three window blocks with at most two blocks of loads in flight: with all
+        // twelve 16-byte loads hoisted the register file (2 x 3*NX matrix entries per row) overflows.
+        float4 q[2][NQ];
+        auto load_block = [&](int j, float4 (&dst)[NQ]) {
+#pragma unroll
+            for (int i = 0; i < NQ; i++) dst[i] = *reinterpret_cast<const float4 *>(w + j * NXP + 4 * i);
+        };
+        auto fma_block = [&](int j, const float4 (&src)[NQ]) {
+#pragma unroll
+            for (int i = 0; i < NQ; i++) {
+                const int c = 4 * i, k = j * NX + c;
+                const int pair = j * ((NX + 1) / 2) + 2 * i;
+#pragma unroll
+                for (int row = 0; row < R; row++) {
+                    acc[row][pair % NCH] =
+                        __ffma2_rn(make_float2(m(row, k), m(row, k + 1)), make_float2(src[i].x, src[i].y), acc[row][pair % NCH]);
+                    if (c + 2 < NX)
+                        acc[row][(pair + 1) % NCH] = __ffma2_rn(make_float2(m(row, k + 2), m(row, k + 3)),
+                                                                make_float2(src[i].z, src[i].w), acc[row][(pair + 1) % NCH]);
+                }
+            }
+        };
+#if FUSED_QBUF == 2
+        load_block(0, q[0]);
+        load_block(1, q[1]);
+        asm volatile("" ::: "memory");
+        fma_block(0, q[0]);
+        load_block(2, q[0]);
+        asm volatile("" ::: "memory");
+        fma_block(1, q[1]);
+        fma_block(2, q[0]);
+#else
+        load_block(0, q[0]);
+        asm volatile("" ::: "memory");
+        fma_block(0, q[0]);
+        asm volatile("" ::: "memory");
+        load_block(1, q[0]);
+        asm volatile("" ::: "memory");
+        fma_block(1, q[0]);
+        asm volatile("" ::: "memory");
+        load_block(2, q[0]);
+        asm volatile("" ::: "memory");
+        fma_block(2, q[0]);
+#endif
+#pragma unroll
+        for (int row = 0; row < R; row++) {
+            float2 s = acc[row][0];
+#pragma unroll
+            for (int ch = 1; ch < NCH; ch++) s = __fadd2_rn(s, acc[row][ch]);
+            y[row] = s.x + s.y;
+        }
+    } else {
+        constexpr int V = Geo<T>::V;
+        constexpr int NCH = 4;
+        T acc[R][NCH];
+#pragma unroll
+        for (int row = 0; row < R; row++)
+#pragma unroll
+            for (int ch = 0; ch < NCH; ch++) acc[row][ch] = (T)0;
+        int idx = 0;
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+#pragma unroll
+            for (int c = 0; c < NX; c += V) {
+                const typename Vec16<T>::type q = *reinterpret_cast<const typename Vec16<T>::type *>(w + j * NXP + c);
+                const int k = j * NX + c;
+                T qq[4];
+                if constexpr (V == 4) { qq[0] = q.x; qq[1] = q.y; qq[2] = q.z; qq[3] = q.w; }
+                else { qq[0] = q.x; qq[1] = q.y; qq[2] = (T)0; qq[3] = (T)0; }
+#pragma unroll
+                for (int e = 0; e < V; e++) {
+                    if (c + e < NX) {
+#pragma unroll
+                        for (int row = 0; row < R; row++) acc[row][(idx + e) % NCH] += m(row, k + e) * qq[e];
+                    }
+                }
+                idx += V;
+            }
+        }
+#pragma unroll
+        for (int row = 0; row < R; row++) y[row] = (acc[row][0] + acc[row][1]) + (acc[row][2] + acc[row][3]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// the kernel
+// ---------------------------------------------------------------------------------------------
+template <typename T, int NX, int R, int PMODE, bool FUSED, bool CLUSTERED, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> a)
+{
+    static_assert(NX % R == 0, "rows per thread must divide the state size");
+    constexpr int NXP = Geo<T>::nxp(NX);
+    constexpr int BSZ = 3 * NX * NX;
+    constexpr int TPB = NX / R;                                                 // threads per block-row
+    constexpr int NWP = round_up(round_up(MAXT, 32) / 32, 2);                   // warp-partial pairs summed per reduction
+    namespace cg = cooperative_groups;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int N = (int)a.N, bpc = (int)a.bpc;
+    const bool use_tma = a.two_buffers != 0;                                    // host decided: sources 16-byte aligned (field reused as the TMA switch)
+    constexpr int nstage = (PMODE == P_REG) ? 2 : 1;                            // staging holds S, and Phi^-1 beside it when both go to registers
+    const FusedPlan plan = make_fused_plan<T>(NX, NXP, bpc, PMODE, nstage);
+    T *red = reinterpret_cast<T *>(smem_raw + plan.red_off);
+    T *cred = reinterpret_cast<T *>(smem_raw + plan.cred_off);
+    T *winA = reinterpret_cast<T *>(smem_raw + plan.winA_off);
+    T *winB = reinterpret_cast<T *>(smem_raw + plan.winB_off);
+    T *stage = reinterpret_cast<T *>(smem_raw + plan.stage_off);
+    T *psm = reinterpret_cast<T *>(smem_raw + plan.psm_off);
+    const uint32_t mbar = smem_u32(smem_raw + plan.mbar_off);
+    const uint32_t mat_bytes_pad = (uint32_t)round_up(bpc * BSZ * (int)sizeof(T), 16);
+    T *stageS = stage;
+    T *stageP = (PMODE == P_SMEM) ? psm : reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(stage) + mat_bytes_pad);
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    int rank = 0, csize = 1;
+    if constexpr (CLUSTERED) {
+        cg::cluster_group cl = cg::this_cluster();
+        rank = (int)cl.block_rank();
+        csize = (int)cl.num_blocks();
+    }
+    const uint32_t cluster_id = blockIdx.x / (uint32_t)csize;
+    const uint32_t n_clusters = gridDim.x / (uint32_t)csize;
+
+    const int lb = t / TPB, ti = t - lb * TPB;            // local block-row, thread inside it
+    const int r0 = ti * R;                                // first row (inside the block) of this thread
+    const int b0 = rank * bpc;                            // first block-row of this CTA
+    const int nb = max(0, min(bpc, N - b0));              // block-rows this CTA really owns
+    const bool active = lb < nb;
+    const int b = b0 + lb;
+    const int last_rank = (N - 1) / bpc;
+
+    auto sync_all = [&]() {
+        if constexpr (CLUSTERED) cg::this_cluster().sync();
+        else __syncthreads();
+    };
+
+    // one-time init
+    for (int i = t; i < (bpc + 2) * NXP; i += blockDim.x) { winA[i] = (T)0; winB[i] = (T)0; }
+    for (int i = t; i < 128; i += blockDim.x) red[i] = (T)0;
+    for (int i = t; i < 64; i += blockDim.x) cred[i] = (T)0;
+    if (t == 0 && use_tma) { mbar_init(mbar, 1); fence_mbar_init(); }
+
+    T *winA_prev = nullptr, *winA_next = nullptr, *winB_prev = nullptr, *winB_next = nullptr;
+    if constexpr (CLUSTERED) {
+        cg::cluster_group cl = cg::this_cluster();
+        if (rank > 0) { winA_prev = cl.map_shared_rank(winA, rank - 1); winB_prev = cl.map_shared_rank(winB, rank - 1); }
+        if (rank + 1 < csize) { winA_next = cl.map_shared_rank(winA, rank + 1); winB_next = cl.map_shared_rank(winB, rank + 1); }
+    }
+    sync_all();
+
+    const int slot = (lb + 1) * NXP + r0;                  // where this thread publishes its R vector elements
+    const int wofs = (active ? lb : 0) * NXP;              // window [x_{b-1} | x_b | x_{b+1}] of this thread's block
+    const bool send_prev = CLUSTERED && active && lb == 0 && rank > 0;
+    const bool send_next = CLUSTERED && active && lb == nb - 1 && rank < last_rank;
+
+    auto put = [&](T *dst, const T (&x)[R]) {
+        if constexpr (R == 2 && sizeof(T) == 4) *reinterpret_cast<float2 *>(dst) = make_float2(x[0], x[1]);
+        else if constexpr (R == 2 && sizeof(T) == 8) *reinterpret_cast<double2 *>(dst) = make_double2(x[0], x[1]);
+        else {
+#pragma unroll
+            for (int i = 0; i < R; i++) dst[i] = x[i];
+        }
+    };
+    auto publish = [&](T *win, T *win_prev, T *win_next, const T (&x)[R]) {
+        if (active) {
+            put(win + slot, x);
+            if constexpr (CLUSTERED) {
+                if (send_prev) put(win_prev + (bpc + 1) * NXP + r0, x);   // right halo of the previous CTA (always full)
+                if (send_next) put(win_next + r0, x);                     // left halo of the next CTA
+            }
+        }
+    };
+
+    // all-thread reduction of a (value0, value1) pair: bit-identical result in every thread of every CTA.
+    // Consecutive reductions alternate between two slots, so a fast warp's next partial can never
+    // overwrite what a slow warp is still summing.
+    int red_slot = 0;
+    auto all_sum = [&](T x0, T x1) -> Pair<T> {
+        Pair<T> p(x0, x1);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) p = p + shfl_xor_pair<T>(p, o);
+        T *rd = red + red_slot * 64;
+        if (lane == 0) {
+            if constexpr (sizeof(T) == 4) *reinterpret_cast<float2 *>(rd + 2 * warp) = make_float2(p.x(), p.y());
+            else *reinterpret_cast<double2 *>(rd + 2 * warp) = make_double2(p.x(), p.y());
+        }
+        __syncthreads();
+        Pair<T> s = pair_tree_sum<T, NWP>(rd);
+        if constexpr (CLUSTERED) {
+            T *cr = cred + red_slot * 32;
+            if (t < csize) {
+                T *dst = cg::this_cluster().map_shared_rank(cr, t);
+                dst[2 * rank] = s.x();
+                dst[2 * rank + 1] = s.y();
+            }
+            cg::this_cluster().sync();
+            s = pair_tree_sum<T, 16>(cr);
+        }
+        red_slot ^= 1;
+        return s;
+    };
+
+    // ---- matrix prefetch (TMA) ----
+    auto issue_prefetch = [&](uint32_t prob) {
+        // one thread: arm the barrier with the byte count, then launch the bulk copies of this CTA's block-rows
+        const uint32_t bytes = (uint32_t)(nb * BSZ * (int)sizeof(T));
+        const T *Sg = a.S + (size_t)prob * a.mat_stride + (size_t)b0 * BSZ;
+        mbar_expect_tx(mbar, (PMODE != P_NONE) ? 2 * bytes : bytes);
+        bulk_g2s(smem_u32(stageS), Sg, bytes, mbar);
+        if constexpr (PMODE != P_NONE) {
+            const T *Pg = a.Pinv + (size_t)prob * a.mat_stride + (size_t)b0 * BSZ;
+            bulk_g2s(smem_u32(stageP), Pg, bytes, mbar);
+        }
+    };
+    uint32_t phase = 0;
+    if (use_tma && t == 0 && nb > 0 && cluster_id < a.batch) issue_prefetch(cluster_id);
+
+    for (uint32_t prob = cluster_id; prob < a.batch; prob += n_clusters) {
+        const size_t vofs = (size_t)prob * a.vec_stride + (size_t)b * NX + r0;
+
+        // vectors first (their latency overlaps the wait for the matrices)
+        T lam[R], gam[R];
+#pragma unroll
+        for (int i = 0; i < R; i++) { lam[i] = (T)0; gam[i] = (T)0; }
+        if (active) {
+#pragma unroll
+            for (int i = 0; i < R; i++) { lam[i] = a.lambda[vofs + i]; gam[i] = __ldg(a.gamma + vofs + i); }
+        }
+
+        // ---- matrices: HBM -> shared (TMA, or cooperative loads) -> registers ----
+        T Sreg[R][3 * NX];
+        T Preg[(PMODE == P_REG) ? R : 1][(PMODE == P_REG) ? 3 * NX : 1];
+        (void)Preg;
+        auto load_rows = [&](T (&M)[R][3 * NX], const T *img) {
+            const T *row = img + (active ? lb * BSZ + r0 : 0);
+#pragma unroll
+            for (int k = 0; k < 3 * NX; k++) {
+                if constexpr (R == 2 && sizeof(T) == 4 && FUSED_LOAD64) {
+                    const float2 q = *reinterpret_cast<const float2 *>(row + k * NX);
+                    M[0][k] = q.x; M[1][k] = q.y;
+                } else if constexpr (R == 2 && sizeof(T) == 8) {
+                    const double2 q = *reinterpret_cast<const double2 *>(row + k * NX);
+                    M[0][k] = q.x; M[1][k] = q.y;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < R; i++) M[i][k] = row[k * NX + i];
+                }
+            }
+            // padding blocks of the layout (left of row 0, right of row N-1) are "never read" in the reference
+            // (include/pcg.cuh:105-106): whatever they hold must not reach the arithmetic
+            const bool kill_left = !active || b == 0, kill_right = !active || b == N - 1, kill_mid = !active;
+#pragma unroll
+            for (int k = 0; k < 3 * NX; k++) {
+                const bool kill = (k < NX) ? kill_left : (k >= 2 * NX) ? kill_right : kill_mid;
+#pragma unroll
+                for (int i = 0; i < R; i++) M[i][k] = kill ? (T)0 : M[i][k];
+            }
+        };
+
+        // Both paths end with the block-row images of S (and Phi^-1) in the staging area; the rows are then pulled
+        // into registers from ONE place (two copies of that code overflow the register file).
+        if (use_tma) {
+            if (nb > 0) { mbar_wait(mbar, phase); phase ^= 1; }
+        } else {
+            const T *Sg = a.S + (size_t)prob * a.mat_stride + (size_t)b0 * BSZ;
+            stage_image<T>(Sg, stageS, nb * BSZ);
+            if constexpr (PMODE != P_NONE) {
+                const T *Pg = a.Pinv + (size_t)prob * a.mat_stride + (size_t)b0 * BSZ;
+                stage_image<T>(Pg, stageP, nb * BSZ);
+            }
+            __syncthreads();
+        }
+        load_rows(Sreg, stageS);
+        if constexpr (PMODE == P_REG) load_rows(Preg, stageP);
+        if constexpr (PMODE == P_SMEM) {
+            // Phi^-1 stays in shared memory: clear its padding blocks in place (this CTA's first / last block-row)
+            __syncthreads();
+            if (b0 == 0) for (int i = t; i < NX * NX; i += blockDim.x) psm[i] = (T)0;
+            if (nb > 0 && b0 + nb == N) for (int i = t; i < NX * NX; i += blockDim.x) psm[(nb - 1) * BSZ + 2 * NX * NX + i] = (T)0;
+        }
+        if (use_tma) {
+            // staging may be overwritten by the next system's matrices once every thread holds its rows
+            __syncthreads();
+            const uint32_t next = prob + n_clusters;
+            if (t == 0 && nb > 0 && next < a.batch && PMODE != P_SMEM) { fence_proxy_async(); issue_prefetch(next); }
+        } else if constexpr (PMODE == P_SMEM) {
+            __syncthreads();
+        }
+        const T *Prow = psm + (active ? lb * BSZ + r0 : 0);
+        (void)Prow;
+
+        auto mv_S = [&](const T *win, T (&y)[R]) {
+            block_row_mv<T, NX, R, false>(Sreg, nullptr, win + wofs, y);
+            if (!active) {
+#pragma unroll
+                for (int i = 0; i < R; i++) y[i] = (T)0;
+            }
+        };
+        auto mv_P = [&](const T *win, T (&y)[R]) {
+            if constexpr (PMODE == P_REG) block_row_mv<T, NX, R, false>(Preg, nullptr, win + wofs, y);
+            else if constexpr (PMODE == P_SMEM) block_row_mv<T, NX, R, true>(Sreg, Prow, win + wofs, y);
+            if (!active) {
+#pragma unroll
+                for (int i = 0; i < R; i++) y[i] = (T)0;
+            }
+        };
+
+        // ---- r = gamma - S*lambda                                               (pcg.cuh:118-126) ----
+        // (the prologue uses whichever window the first loop publish does NOT touch, which saves a barrier)
+        T res[R], rt[R], w[R], p[R];
+        constexpr bool PRO_B = FUSED && PMODE != P_NONE;
+        if constexpr (PRO_B) publish(winB, winB_prev, winB_next, lam);
+        else publish(winA, winA_prev, winA_next, lam);
+        sync_all();
+        mv_S(PRO_B ? winB : winA, w);
+#pragma unroll
+        for (int i = 0; i < R; i++) res[i] = gam[i] - w[i];
+
+        uint32_t it = 0;
+        bool hit_max = true;
+
+        if constexpr (FUSED) {
+            // ---------------- Chronopoulos-Gear form: one reduction per iteration ----------------
+            T s[R];
+#pragma unroll
+            for (int i = 0; i < R; i++) { p[i] = (T)0; s[i] = (T)0; }
+            T rcp_gamma = (T)0, rcp_alpha = (T)0;
+            for (;;) {
+                if constexpr (PMODE != P_NONE) {
+                    publish(winA, winA_prev, winA_next, res);
+                    sync_all();
+                    mv_P(winA, rt);                        // r~ = Phi^-1 r
+                } else {
+#pragma unroll
+                    for (int i = 0; i < R; i++) rt[i] = res[i];
+                }
+                publish(winB, winB_prev, winB_next, rt);
+                sync_all();
+                mv_S(winB, w);                             // w = S r~
+                T g = (T)0, d = (T)0;
+#pragma unroll
+                for (int i = 0; i < R; i++) { g += res[i] * rt[i]; d += w[i] * rt[i]; }
+                const Pair<T> gd = all_sum(g, d);          // gamma = r.r~ , delta = w.r~
+                const T gamma = gd.x(), delta = gd.y();
+                if (it > 0 && abs_t(gamma) < a.tol) { hit_max = false; break; }   // reference exit test (pcg.cuh:195)
+                if (it == a.max_iter) break;
+                T beta, alpha;
+                if (it == 0) { beta = (T)0; alpha = gamma / delta; }
+                else {
+                    beta = gamma * rcp_gamma;                                      // gamma / gamma_old
+                    alpha = gamma / (delta - beta * (gamma * rcp_alpha));          // gamma / (delta - beta*gamma/alpha_old)
+                }
+#pragma unroll
+                for (int i = 0; i < R; i++) {
+                    p[i] = rt[i] + beta * p[i];
+                    s[i] = w[i] + beta * s[i];
+                    lam[i] += alpha * p[i];
+                    res[i] -= alpha * s[i];
+                }
+                rcp_gamma = (T)1 / gamma;
+                rcp_alpha = (T)1 / alpha;
+                ++it;
+            }
+        } else {
+            // ---------------- textbook order (reference include/pcg.cuh:131-208) ----------------
+            if constexpr (PMODE != P_NONE) {
+                publish(winB, winB_prev, winB_next, res);
+                sync_all();
+                mv_P(winB, rt);
+            } else {
+#pragma unroll
+                for (int i = 0; i < R; i++) rt[i] = res[i];
+            }
+            T e0 = (T)0;
+#pragma unroll
+            for (int i = 0; i < R; i++) { p[i] = rt[i]; e0 += res[i] * rt[i]; }
+            T eta = all_sum(e0, (T)0).x();
+            for (; it < a.max_iter; ++it) {
+                publish(winA, winA_prev, winA_next, p);
+                sync_all();
+                mv_S(winA, w);                             // upsilon = S p
+                T v0 = (T)0;
+#pragma unroll
+                for (int i = 0; i < R; i++) v0 += p[i] * w[i];
+                const T v = all_sum(v0, (T)0).x();
+                const T alpha = eta / v;
+#pragma unroll
+                for (int i = 0; i < R; i++) { lam[i] += alpha * p[i]; res[i] -= alpha * w[i]; }
+                if constexpr (PMODE != P_NONE) {
+                    publish(winB, winB_prev, winB_next, res);
+                    sync_all();
+                    mv_P(winB, rt);                        // r~ = Phi^-1 r
+                } else {
+#pragma unroll
+                    for (int i = 0; i < R; i++) rt[i] = res[i];
+                }
+                T e1 = (T)0;
+#pragma unroll
+                for (int i = 0; i < R; i++) e1 += res[i] * rt[i];
+                const T eta_new = all_sum(e1, (T)0).x();
+                if (abs_t(eta_new) < a.tol) { ++it; hit_max = false; break; }
+                const T beta = eta_new / eta;
+                eta = eta_new;
+#pragma unroll
+                for (int i = 0; i < R; i++) p[i] = rt[i] + beta * p[i];
+            }
+        }
+
+        // ---- outputs                                                            (pcg.cuh:212-215) ----
+        if (active) {
+#pragma unroll
+            for (int i = 0; i < R; i++) a.lambda[vofs + i] = lam[i];
+        }
+        if (rank == 0 && t == 0) {
+            if (a.iters) a.iters[prob] = it;
+            if (a.exits) a.exits[prob] = hit_max ? 1 : 0;
+        }
+        // No barrier here: every read of this system's windows and staging happened before the barrier inside
+        // the last reduction, and the partial-sum slots alternate.
+    }
+    if constexpr (CLUSTERED) cg::this_cluster().sync();   // no CTA may exit while a neighbour can still store into it
+}
+
+}  // namespace gbdpcg

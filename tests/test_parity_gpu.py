@@ -387,3 +387,33 @@ def test_cpp_examples_run(example, iters, tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     m = re.search(r"(\d+) iterations", r.stdout)
     assert m and (iters is None or int(m.group(1)) == iters), r.stdout
+
+
+# ---------------------------------------------------------------------------------------------
+# kernel-selection flags: every recurrence / staging / generation variant solves the same systems
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("flag", ["TEXTBOOK", "FUSED", "NO_TMA", "LEGACY_ROWS"])
+@pytest.mark.parametrize("name,precond", [("C2", "stair"), ("C2", "identity"), ("C3", "stair"), ("C4", "jacobi")])
+def test_kernel_variant_flags(flag, name, precond):
+    S, P, gam, nx, N, tol, max_iter = make_system(name, precond)
+    lam0 = np.zeros(N * nx, dtype=S.dtype)
+    flags = getattr(g._lib, "FLAG_" + flag)
+    info = g.plan_query(nx, N, S.dtype, P is not None, g.pcg_config(flags=flags))
+    assert ("pcg_rows" in info["kernel"]) == (flag == "LEGACY_ROWS")
+    lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter, flags=flags)
+    assert not ex
+    check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex)
+
+
+def test_unaligned_device_pointers_fall_back_from_tma():
+    """S / Phi^-1 at addresses that are only 4-byte aligned: the bulk-copy path must not be used, results unchanged."""
+    torch = _torch()
+    S, P, gam, nx, N, tol, max_iter = make_system("C2", "stair")
+    lam_a, it_a, _ = gpu_solve(S, P, gam, np.zeros(N * nx, np.float32), nx, N, tol, max_iter)
+    pad = lambda a: torch.from_numpy(np.concatenate([np.zeros(1, a.dtype), a])).cuda()[1:]
+    d_S, d_P, d_g = pad(S), pad(P), pad(gam)
+    assert d_S.data_ptr() % 16 == 4
+    d_l = torch.zeros(N * nx, dtype=torch.float32, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter)
+    it = g.api._solve_dev(nx, N, d_S, d_P, d_g, d_l, config=cfg)
+    assert it == it_a and np.array_equal(d_l.cpu().numpy(), lam_a)
