@@ -14,6 +14,7 @@
 #include "gbdpcg.h"
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
+#include "pcg_slab.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
 
@@ -116,7 +117,9 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
         for (int ip = 0; ip < n_pm; ip++) {
             for (int i = 0; i < cnt; i++) {
                 const FusedVariant *v = &tab[i];
-                const int threads = round_up(bpc * ((int)nx / v->rpt), 32);
+                if (v->slab && !(cfg.flags & GBDPCG_FLAG_SLAB_LAYOUT)) continue;
+                if (v->slab && v->pmode == P_REG && v->maxt <= 32) continue;    // slab P_REG not buildable for this nx
+                const int threads = v->slab ? slab_threads((int)nx, bpc) : round_up(bpc * ((int)nx / v->rpt), 32);
                 if (v->clustered != (cl > 1) || v->pmode != pm_opts[ip] || threads > v->maxt) continue;
                 const size_t smem = make_fused_plan<T>((int)nx, v->nxp, bpc, v->pmode, v->pmode == P_REG ? 2 : 1).total;
                 if (smem > kMaxDynSmem) continue;

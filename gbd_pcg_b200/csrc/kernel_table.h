@@ -31,6 +31,7 @@ struct FusedVariant {
     int nx;
     int is_f64;
     int rpt;         // rows per thread
+    int slab;        // 1: column-slab layout (pcg_slab.cuh), 0: row layout (pcg_fused.cuh)
     int clustered;
     int pmode;
     int fused;       // 1: single-reduction (Chronopoulos-Gear) order, 0: the reference's two-reduction order

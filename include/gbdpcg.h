@@ -67,6 +67,8 @@ typedef struct gbdpcg_config {
 #define GBDPCG_FLAG_FUSED 0x10u        /* single-reduction (Chronopoulos-Gear) form of the same recurrence
                                           (default for fp32)                                                  */
 #define GBDPCG_FLAG_LEGACY_ROWS 0x20u  /* first-generation one-row-per-thread kernel (kept for A/B measurements) */
+#define GBDPCG_FLAG_SLAB_LAYOUT 0x80u  /* fp32: column-slab ownership of the matrix entries (pcg_slab.cuh); fewer shared-memory
+                                          bytes per mat-vec, more instructions -- measured slower on C2, kept for A/B */
 #define GBDPCG_FLAG_NO_TMA 0x40u       /* stage matrices with ordinary loads instead of cp.async.bulk           */
 
 GBDPCG_API void gbdpcg_config_default(gbdpcg_config *cfg);

@@ -392,7 +392,7 @@ def test_cpp_examples_run(example, iters, tmp_path):
 # ---------------------------------------------------------------------------------------------
 # kernel-selection flags: every recurrence / staging / generation variant solves the same systems
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("flag", ["TEXTBOOK", "FUSED", "NO_TMA", "LEGACY_ROWS"])
+@pytest.mark.parametrize("flag", ["TEXTBOOK", "FUSED", "NO_TMA", "LEGACY_ROWS", "SLAB_LAYOUT"])
 @pytest.mark.parametrize("name,precond", [("C2", "stair"), ("C2", "identity"), ("C3", "stair"), ("C4", "jacobi")])
 def test_kernel_variant_flags(flag, name, precond):
     S, P, gam, nx, N, tol, max_iter = make_system(name, precond)
@@ -400,6 +400,8 @@ def test_kernel_variant_flags(flag, name, precond):
     flags = getattr(g._lib, "FLAG_" + flag)
     info = g.plan_query(nx, N, S.dtype, P is not None, g.pcg_config(flags=flags))
     assert ("pcg_rows" in info["kernel"]) == (flag == "LEGACY_ROWS")
+    if flag == "SLAB_LAYOUT" and S.dtype == np.float32 and info["pinv_mode"] != 2:
+        assert "pcg_slab" in info["kernel"]
     lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter, flags=flags)
     assert not ex
     check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex)
