@@ -92,6 +92,17 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
+def measured_traffic(batch):
+    """dram__bytes_read + dram__bytes_write of ONE launch of the batched kernel from the committed ncu --set full
+    capture (profiles/traffic.json, written by scripts/summarize_profiles.py); None when no capture matches this batch."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        t = json.load(open(p))
+        return float(t["dram_bytes_per_launch"]) if int(t["batch"]) == int(batch) else None
+    except Exception:
+        return None
+
+
 def dist_env():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -308,7 +319,8 @@ def run_ours(args):
                     "steps": e2e_steps, "api": "gbdpcg_solve_batched_host_f32 (pinned host buffers, chunked 2-stream overlap)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "bytes_per_solve": bytes_per_solve,
+                         "traffic": measured_traffic(batch), "algorithmic_bytes_per_launch": bytes_per_solve * batch,
+                         "peak_source": peak_src, "bytes_per_solve": bytes_per_solve,
                          "kernel_ms": launch_s * 1e3},
             "clocks": clocks,
             "strong_scaling": {"value": strong_value, "unit": "solves/s", "total_batch": batch,
