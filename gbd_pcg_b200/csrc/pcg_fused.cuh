@@ -360,11 +360,13 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
     for (int i = t; i < 64; i += blockDim.x) cred[i] = (T)0;
     if (t == 0 && use_tma) { mbar_init(mbar, 1); fence_mbar_init(); }
 
-    T *winA_prev = nullptr, *winA_next = nullptr, *winB_prev = nullptr, *winB_next = nullptr;
+    // window B sits at the same offset from window A in every CTA, so one pair of remote pointers serves both
+    const int wdelta = (int)((plan.winB_off - plan.winA_off) / sizeof(T));
+    T *winA_prev = nullptr, *winA_next = nullptr;
     if constexpr (CLUSTERED) {
         cg::cluster_group cl = cg::this_cluster();
-        if (rank > 0) { winA_prev = cl.map_shared_rank(winA, rank - 1); winB_prev = cl.map_shared_rank(winB, rank - 1); }
-        if (rank + 1 < csize) { winA_next = cl.map_shared_rank(winA, rank + 1); winB_next = cl.map_shared_rank(winB, rank + 1); }
+        if (rank > 0) winA_prev = cl.map_shared_rank(winA, rank - 1);
+        if (rank + 1 < csize) winA_next = cl.map_shared_rank(winA, rank + 1);
     }
     sync_all();
 
@@ -381,12 +383,13 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             for (int i = 0; i < R; i++) dst[i] = x[i];
         }
     };
-    auto publish = [&](T *win, T *win_prev, T *win_next, const T (&x)[R]) {
+    auto publish = [&](const bool toB, const T (&x)[R]) {
+        const int wo = toB ? wdelta : 0;
         if (active) {
-            put(win + slot, x);
+            put(winA + wo + slot, x);
             if constexpr (CLUSTERED) {
-                if (send_prev) put(win_prev + (bpc + 1) * NXP + r0, x);   // right halo of the previous CTA (always full)
-                if (send_next) put(win_next + r0, x);                     // left halo of the next CTA
+                if (send_prev) put(winA_prev + wo + (bpc + 1) * NXP + r0, x);   // right halo of the previous CTA (always full)
+                if (send_next) put(winA_next + wo + r0, x);                     // left halo of the next CTA
             }
         }
     };
@@ -415,6 +418,26 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             }
             cg::this_cluster().sync();
             s = pair_tree_sum<T, 16>(cr);
+        }
+        red_slot ^= 1;
+        return s;
+    };
+
+    // single-value form for the two-reduction (textbook) order: half the shuffles and half the partials
+    auto all_sum1 = [&](T x) -> T {
+        T ws = warp_allsum(x);
+        T *rd = red + red_slot * 64;
+        if (lane == 0) rd[warp] = ws;
+        __syncthreads();
+        T s = tree_sum_smem<T, round_up(round_up(MAXT, 32) / 32, Geo<T>::V)>(rd);
+        if constexpr (CLUSTERED) {
+            T *cr = cred + red_slot * 32;
+            if (t < csize) {
+                T *dst = cg::this_cluster().map_shared_rank(cr, t);
+                dst[rank] = s;
+            }
+            cg::this_cluster().sync();
+            s = tree_sum_smem<T, 16>(cr);
         }
         red_slot ^= 1;
         return s;
@@ -529,8 +552,8 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         // (the prologue uses whichever window the first loop publish does NOT touch, which saves a barrier)
         T res[R], rt[R], w[R], p[R];
         constexpr bool PRO_B = FUSED && PMODE != P_NONE;
-        if constexpr (PRO_B) publish(winB, winB_prev, winB_next, lam);
-        else publish(winA, winA_prev, winA_next, lam);
+        if constexpr (PRO_B) publish(true, lam);
+        else publish(false, lam);
         sync_all();
         mv_S(PRO_B ? winB : winA, w);
 #pragma unroll
@@ -547,14 +570,14 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             T rcp_gamma = (T)0, rcp_alpha = (T)0;
             for (;;) {
                 if constexpr (PMODE != P_NONE) {
-                    publish(winA, winA_prev, winA_next, res);
+                    publish(false, res);
                     sync_all();
                     mv_P(winA, rt);                        // r~ = Phi^-1 r
                 } else {
 #pragma unroll
                     for (int i = 0; i < R; i++) rt[i] = res[i];
                 }
-                publish(winB, winB_prev, winB_next, rt);
+                publish(true, rt);
                 sync_all();
                 mv_S(winB, w);                             // w = S r~
                 T g = (T)0, d = (T)0;
@@ -584,7 +607,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         } else {
             // ---------------- textbook order (reference include/pcg.cuh:131-208) ----------------
             if constexpr (PMODE != P_NONE) {
-                publish(winB, winB_prev, winB_next, res);
+                publish(true, res);
                 sync_all();
                 mv_P(winB, rt);
             } else {
@@ -594,20 +617,20 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             T e0 = (T)0;
 #pragma unroll
             for (int i = 0; i < R; i++) { p[i] = rt[i]; e0 += res[i] * rt[i]; }
-            T eta = all_sum(e0, (T)0).x();
+            T eta = all_sum1(e0);
             for (; it < a.max_iter; ++it) {
-                publish(winA, winA_prev, winA_next, p);
+                publish(false, p);
                 sync_all();
                 mv_S(winA, w);                             // upsilon = S p
                 T v0 = (T)0;
 #pragma unroll
                 for (int i = 0; i < R; i++) v0 += p[i] * w[i];
-                const T v = all_sum(v0, (T)0).x();
+                const T v = all_sum1(v0);
                 const T alpha = eta / v;
 #pragma unroll
                 for (int i = 0; i < R; i++) { lam[i] += alpha * p[i]; res[i] -= alpha * w[i]; }
                 if constexpr (PMODE != P_NONE) {
-                    publish(winB, winB_prev, winB_next, res);
+                    publish(true, res);
                     sync_all();
                     mv_P(winB, rt);                        // r~ = Phi^-1 r
                 } else {
@@ -617,7 +640,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
                 T e1 = (T)0;
 #pragma unroll
                 for (int i = 0; i < R; i++) e1 += res[i] * rt[i];
-                const T eta_new = all_sum(e1, (T)0).x();
+                const T eta_new = all_sum1(e1);
                 if (abs_t(eta_new) < a.tol) { ++it; hit_max = false; break; }
                 const T beta = eta_new / eta;
                 eta = eta_new;

@@ -34,7 +34,7 @@ constexpr int RPT = INST_RPT;
 // working state; the SM has 64 K registers, a thread at most 255.
 constexpr int regs_needed(int nx, int nmat_reg)
 {
-    return (int)(sizeof(InstT) / 4) * 3 * nx * RPT * nmat_reg + (sizeof(InstT) == 8 ? 72 : 56);
+    return (int)(sizeof(InstT) / 4) * 3 * nx * RPT * nmat_reg + (sizeof(InstT) == 8 ? (nmat_reg == 2 ? 72 : 96) : 56);
 }
 // The register file is split over the 4 SM sub-partitions (16 K registers each) and warps are dealt to them
 // round-robin, so what bounds registers per thread is warps per sub-partition: 512 / regs, whole warps.
