@@ -9,11 +9,14 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgbdpcg.so")
+# GBDPCG_LIB: load an experiment build of the same library (scripts/, A/B runs); the default is the in-tree build
+LIB_PATH = os.environ.get("GBDPCG_LIB") or os.path.join(_HERE, "libgbdpcg.so")
 
 OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM = 0, -1, -2, -3, -4
 FLAG_FORCE_GENERIC, FLAG_PINV_SMEM, FLAG_PINV_REG = 0x1, 0x2, 0x4
 FLAG_TEXTBOOK, FLAG_FUSED, FLAG_LEGACY_ROWS, FLAG_NO_TMA, FLAG_SLAB_LAYOUT = 0x8, 0x10, 0x20, 0x40, 0x80
+FLAG_BUILD_JACOBI, FLAG_BUILD_STAIR = 0x100, 0x200
+PINV_IDENTITY, PINV_JACOBI, PINV_STAIR = 0, 1, 2
 
 
 class GbdpcgError(RuntimeError):
@@ -56,6 +59,8 @@ for _s in ("f32", "f64"):
     SIGNATURES[f"gbdpcg_solve_dev_sync_{_s}"] = (C.c_int, [_VP] * 5 + [_U32, _U32, _CFG, C.POINTER(_U32), C.POINTER(_I32), _VP])
     SIGNATURES[f"gbdpcg_solve_batched_dev_{_s}"] = (C.c_int, [_VP] * 5 + [_U32, _U32, _U32, _CFG, _VP, _VP, _VP])
     SIGNATURES[f"gbdpcg_solve_batched_host_{_s}"] = (C.c_int, [_VP] * 5 + [_U32, _U32, _U32, _CFG, _VP, _VP])
+    SIGNATURES[f"gbdpcg_build_pinv_dev_{_s}"] = (C.c_int, [_VP] * 3 + [_U32, _U32, _U32, C.c_int, _VP])
+    SIGNATURES[f"gbdpcg_build_pinv_host_{_s}"] = (C.c_int, [_VP] * 3 + [_U32, _U32, _U32, C.c_int])
 
 _lib = None
 

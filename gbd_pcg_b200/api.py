@@ -115,7 +115,8 @@ def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pi
     (the reference returns 1 unconditionally, include/interface.cuh:88 -- a defect this build does not keep).
     ``h_Pinv`` (extension) supplies Phi^-1; it is used only when ``config.empty_pinv == 0``."""
     config = config or pcg_config()
-    if not config.empty_pinv and h_Pinv is None:
+    builds = bool(config.flags & (_lib.FLAG_BUILD_JACOBI | _lib.FLAG_BUILD_STAIR))
+    if not config.empty_pinv and h_Pinv is None and not builds:
         # the reference prints this and carries on with an uninitialised d_Pinv (interface.cuh:33-34,45-46)
         print("This api can only be called with no preconditioner")
     suf = _suffix(h_S.dtype)
@@ -196,6 +197,39 @@ def solve_batched_host(h_S, h_Pinv, h_gamma, h_lambda, state_size, knot_points, 
                  _host(h_gamma, h_S.dtype, vs, "h_gamma"), _host(h_lambda, h_S.dtype, vs, "h_lambda", True),
                  nx, N, B, C.byref(cfg), iters.ctypes.data_as(C.c_void_p), exits.ctypes.data_as(C.c_void_p)))
     return iters, exits.astype(bool)
+
+
+PINV_KINDS = {"identity": _lib.PINV_IDENTITY, "jacobi": _lib.PINV_JACOBI, "stair": _lib.PINV_STAIR}
+BUILD_FLAGS = {"jacobi": _lib.FLAG_BUILD_JACOBI, "stair": _lib.FLAG_BUILD_STAIR}
+
+
+def _kind(kind) -> int:
+    if isinstance(kind, str):
+        if kind not in PINV_KINDS:
+            raise ValueError(f"preconditioner kind must be one of {sorted(PINV_KINDS)}")
+        return PINV_KINDS[kind]
+    return int(kind)
+
+
+def build_pinv_dev(state_size, knot_points, batch, d_S, d_Pinv, kind="stair", stream=None):
+    """Enqueue the construction of Phi^-1 (identity / block-Jacobi / symmetric stair) from ``d_S`` into ``d_Pinv``
+    for ``batch`` problem-major systems (the reference never builds one,
+    include/interface.cuh:33-34,45-46)."""
+    suf = _torch_dtype_suffix(d_S)
+    f = getattr(_lib.lib(), f"gbdpcg_build_pinv_dev_{suf}")
+    _lib.check(f(None, _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv"), int(state_size), int(knot_points), int(batch),
+                 _kind(kind), _stream_ptr(stream)))
+
+
+def build_pinv_host(h_S, state_size, knot_points, batch=1, kind="stair"):
+    """Blocking host form: returns Phi^-1 (numpy, same dtype and layout as ``h_S``), computed on the GPU."""
+    suf = _suffix(h_S.dtype)
+    nx, N, B = int(state_size), int(knot_points), int(batch)
+    ms = 3 * N * nx * nx * B
+    out = np.empty(ms, dtype=h_S.dtype)
+    f = getattr(_lib.lib(), f"gbdpcg_build_pinv_host_{suf}")
+    _lib.check(f(None, _host(h_S, h_S.dtype, ms, "h_S"), out.ctypes.data_as(C.c_void_p), nx, N, B, _kind(kind)))
+    return out.reshape(h_S.shape) if h_S.size == ms else out
 
 
 def plan_query(state_size, knot_points, dtype=np.float32, has_pinv=True, config=None) -> dict:

@@ -17,6 +17,7 @@
 #include "pcg_slab.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
+#include "pinv_build.h"
 
 namespace gbdpcg {
 
@@ -407,6 +408,33 @@ static int get_ws(gbdpcg_workspace *user, gbdpcg_workspace **out)
 // ------------------------------------------------------------------------------------------------
 static inline bool use_pinv(const void *Pinv, const gbdpcg_config *cfg) { return Pinv != nullptr && cfg->empty_pinv == 0; }
 
+// GBDPCG_FLAG_BUILD_*: the host entry points form Phi^-1 from S on the device instead of taking it from the caller
+static inline int build_kind(const gbdpcg_config *cfg)
+{
+    if (cfg->flags & GBDPCG_FLAG_BUILD_STAIR) return GBDPCG_PINV_STAIR;
+    if (cfg->flags & GBDPCG_FLAG_BUILD_JACOBI) return GBDPCG_PINV_JACOBI;
+    return -1;
+}
+
+template <typename T>
+static int build_pinv_dev(const T *S, T *Pinv, uint32_t nx, uint32_t N, uint32_t batch, int kind, void *stream)
+{
+    if (!S || !Pinv) return fail(GBDPCG_ERR_INVALID, "S and Pinv must not be NULL");
+    if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
+    if (kind != GBDPCG_PINV_IDENTITY && kind != GBDPCG_PINV_JACOBI && kind != GBDPCG_PINV_STAIR)
+        return fail(GBDPCG_ERR_INVALID, "preconditioner kind must be GBDPCG_PINV_IDENTITY, _JACOBI or _STAIR");
+    if ((uint64_t)nx * N > (1u << 24)) return fail(GBDPCG_ERR_UNSUPPORTED, "system too large");
+    if (batch == 0) return GBDPCG_OK;
+    const int rc = launch_pinv_build<T>(S, Pinv, nx, N, batch, kind, (cudaStream_t)stream, nullptr, false);
+    if (rc == -3) return fail(GBDPCG_ERR_UNSUPPORTED, "state size %u is too large for the preconditioner builder", nx);
+    if (rc != 0) return fail_cuda((cudaError_t)rc, "launch_pinv_build", __LINE__);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
+template <typename T>
+static int build_pinv_host(gbdpcg_workspace *user_ws, const T *hS, T *hP, uint32_t nx, uint32_t N, uint32_t batch, int kind);
+
 template <typename T>
 static int solve_batched_dev(const T *S, const T *Pinv, const T *gamma, T *lambda, uint32_t nx, uint32_t N, uint32_t batch,
                              const gbdpcg_config *cfg, uint32_t *d_iters, uint8_t *d_exits, void *stream)
@@ -446,7 +474,8 @@ static int solve_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const
     rc = get_ws(user_ws, &w);
     if (rc) return rc;
     std::lock_guard<std::mutex> lk(w->mu);
-    const bool has_p = use_pinv(hP, cfg);
+    const int bk = build_kind(cfg);
+    const bool has_p = bk >= 0 || use_pinv(hP, cfg);
     const size_t mb = sizeof(T) * 3 * (size_t)N * nx * nx, vb = sizeof(T) * (size_t)N * nx;
     if ((rc = ws_reserve(w, 0, mb))) return rc;
     if (has_p && (rc = ws_reserve(w, 1, mb))) return rc;
@@ -454,11 +483,14 @@ static int solve_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const
     if ((rc = ws_reserve(w, 3, vb))) return rc;
     cudaStream_t st = w->streams[0];
     CK(cudaMemcpyAsync(w->dbuf[0], hS, mb, cudaMemcpyHostToDevice, st));
-    if (has_p) CK(cudaMemcpyAsync(w->dbuf[1], hP, mb, cudaMemcpyHostToDevice, st));
+    if (bk >= 0) { if ((rc = build_pinv_dev<T>((const T *)w->dbuf[0], (T *)w->dbuf[1], nx, N, 1, bk, st))) return rc; }
+    else if (has_p) CK(cudaMemcpyAsync(w->dbuf[1], hP, mb, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(w->dbuf[2], hg, vb, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(w->dbuf[3], hl, vb, cudaMemcpyHostToDevice, st));
+    gbdpcg_config c1 = *cfg;
+    if (bk >= 0) c1.empty_pinv = 0;
     rc = solve_batched_dev<T>((const T *)w->dbuf[0], has_p ? (const T *)w->dbuf[1] : nullptr, (const T *)w->dbuf[2], (T *)w->dbuf[3],
-                              nx, N, 1, cfg, w->hd_iters, w->hd_exit, st);
+                              nx, N, 1, &c1, w->hd_iters, w->hd_exit, st);
     if (rc) return rc;
     CK(cudaMemcpyAsync(hl, w->dbuf[3], vb, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
@@ -481,7 +513,8 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     rc = get_ws(user_ws, &w);
     if (rc) return rc;
     std::lock_guard<std::mutex> lk(w->mu);
-    const bool has_p = use_pinv(hP, cfg);
+    const int bk = build_kind(cfg);
+    const bool has_p = bk >= 0 || use_pinv(hP, cfg);
     const size_t me = 3 * (size_t)N * nx * nx, ve = (size_t)N * nx;
     if ((rc = ws_reserve(w, 0, sizeof(T) * me * batch))) return rc;
     if (has_p && (rc = ws_reserve(w, 1, sizeof(T) * me * batch))) return rc;
@@ -507,7 +540,8 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
         const size_t n = (batch - o < chunk) ? batch - o : chunk;
         cudaStream_t st = w->streams[ci & 1];
         CK(cudaMemcpyAsync(dS + o * me, hS + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
-        if (has_p) CK(cudaMemcpyAsync(dP + o * me, hP + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
+        if (bk >= 0) { if ((rc = build_pinv_dev<T>(dS + o * me, dP + o * me, nx, N, (uint32_t)n, bk, st))) return rc; }
+        else if (has_p) CK(cudaMemcpyAsync(dP + o * me, hP + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(dg + o * ve, hg + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(dl + o * ve, hl + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
         rc = launch<T>(p, dS + o * me, has_p ? dP + o * me : nullptr, dg + o * ve, dl + o * ve, nx, N, (uint32_t)n, *cfg,
@@ -519,6 +553,27 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     }
     CK(cudaStreamSynchronize(w->streams[0]));
     CK(cudaStreamSynchronize(w->streams[1]));
+    return GBDPCG_OK;
+}
+
+template <typename T>
+static int build_pinv_host(gbdpcg_workspace *user_ws, const T *hS, T *hP, uint32_t nx, uint32_t N, uint32_t batch, int kind)
+{
+    if (!hS || !hP) return fail(GBDPCG_ERR_INVALID, "S and Pinv must not be NULL");
+    if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
+    if (batch == 0) return GBDPCG_OK;
+    gbdpcg_workspace *w;
+    int rc = get_ws(user_ws, &w);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(w->mu);
+    const size_t mb = sizeof(T) * 3 * (size_t)N * nx * nx * batch;
+    if ((rc = ws_reserve(w, 0, mb))) return rc;
+    if ((rc = ws_reserve(w, 1, mb))) return rc;
+    cudaStream_t st = w->streams[0];
+    CK(cudaMemcpyAsync(w->dbuf[0], hS, mb, cudaMemcpyHostToDevice, st));
+    if ((rc = build_pinv_dev<T>((const T *)w->dbuf[0], (T *)w->dbuf[1], nx, N, batch, kind, st))) return rc;
+    CK(cudaMemcpyAsync(hP, w->dbuf[1], mb, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return GBDPCG_OK;
 }
 
@@ -601,7 +656,12 @@ void gbdpcg_workspace_destroy(gbdpcg_workspace *ws)
     { return solve_batched_dev<T>(S, P, g, l, nx, N, batch, cfg, d_iters, d_mie, stream); }                                         \
     int gbdpcg_solve_batched_host_##SUF(gbdpcg_workspace *ws, const T *S, const T *P, const T *g, T *l, uint32_t nx, uint32_t N,    \
                                         uint32_t batch, const gbdpcg_config *cfg, uint32_t *h_iters, uint8_t *h_mie)                \
-    { return solve_batched_host<T>(ws, S, P, g, l, nx, N, batch, cfg, h_iters, h_mie); }
+    { return solve_batched_host<T>(ws, S, P, g, l, nx, N, batch, cfg, h_iters, h_mie); }                                            \
+    int gbdpcg_build_pinv_dev_##SUF(gbdpcg_workspace *, const T *S, T *P, uint32_t nx, uint32_t N, uint32_t batch, int kind,        \
+                                    void *stream)                                                                                   \
+    { return build_pinv_dev<T>(S, P, nx, N, batch, kind, stream); }                                                                 \
+    int gbdpcg_build_pinv_host_##SUF(gbdpcg_workspace *ws, const T *S, T *P, uint32_t nx, uint32_t N, uint32_t batch, int kind)     \
+    { return build_pinv_host<T>(ws, S, P, nx, N, batch, kind); }
 
 DEFINE_TYPED(f32, float)
 DEFINE_TYPED(f64, double)

@@ -44,6 +44,9 @@
 #ifndef FUSED_QBUF
 #define FUSED_QBUF 2
 #endif
+#ifndef FUSED_SCALAR_FMA
+#define FUSED_SCALAR_FMA 0   // 1: fp32 mat-vec with scalar FFMA (A/B against the packed FFMA2 form)
+#endif
 
 namespace gbdpcg {
 
@@ -210,7 +213,7 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
         if constexpr (SMEM_M) return Ms[k * NX + row];
         else return M[row][k];
     };
-    if constexpr (sizeof(T) == 4 && NX % 2 == 0) {
+    if constexpr (sizeof(T) == 4 && NX % 2 == 0 && !FUSED_SCALAR_FMA) {
         constexpr int NCH = (R == 1) ? 4 : FUSED_NCH_R2;  // independent FFMA2 chains per row
         constexpr int NQ = (NX + 3) / 4;       // 16-byte loads per window block
         float2 acc[R][NCH];

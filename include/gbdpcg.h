@@ -70,6 +70,12 @@ typedef struct gbdpcg_config {
 #define GBDPCG_FLAG_SLAB_LAYOUT 0x80u  /* fp32: column-slab ownership of the matrix entries (pcg_slab.cuh); fewer shared-memory
                                           bytes per mat-vec, more instructions -- measured slower on C2, kept for A/B */
 #define GBDPCG_FLAG_NO_TMA 0x40u       /* stage matrices with ordinary loads instead of cp.async.bulk           */
+/* Host entry points only: form Phi^-1 from S ON THE DEVICE (gbdpcg_build_pinv_*) instead of taking it from the caller;
+ * the Pinv argument and empty_pinv are then ignored.  This is what makes the reference's own host signature
+ * solvePCG<T>(h_S, h_gamma, h_lambda, ...) -- which has no Pinv parameter (include/interface.cuh:24-31) -- a
+ * PRECONDITIONED solve, and it halves the bytes a host-resident batch has to push over PCIe. */
+#define GBDPCG_FLAG_BUILD_JACOBI 0x100u
+#define GBDPCG_FLAG_BUILD_STAIR 0x200u
 
 GBDPCG_API void gbdpcg_config_default(gbdpcg_config *cfg);
 
@@ -131,6 +137,26 @@ GBDPCG_API int gbdpcg_solve_batched_host_f32(gbdpcg_workspace *ws, const float *
 GBDPCG_API int gbdpcg_solve_batched_host_f64(gbdpcg_workspace *ws, const double *h_S, const double *h_Pinv, const double *h_gamma,
                                   double *h_lambda, uint32_t nx, uint32_t N, uint32_t batch, const gbdpcg_config *cfg,
                                   uint32_t *h_iters, uint8_t *h_max_iter_exit);
+
+/* -- preconditioner construction on the device (no reference entry point: the reference
+ *    carries glass::invertMatrix / glass::gemm / load_block_bd (GLASS/src/L3/inv.cuh:6-37, GLASS/src/L3/gemm.cuh:9-103,
+ *    include/utils.cuh:96-161) for exactly this and never calls them).  From S in the compressed layout:
+ *      GBDPCG_PINV_IDENTITY  diag blocks = I
+ *      GBDPCG_PINV_JACOBI    Phi^-1_kk = S_kk^-1                      (Gauss-Jordan without pivoting, inv.cuh order)
+ *      GBDPCG_PINV_STAIR     + Phi^-1_{k,k+-1} = -S_kk^-1 S_{k,k+-1} S_{k+-1,k+-1}^-1   (symmetric stair)
+ *    Padding blocks of the output are zero.  `batch` problem-major systems.  _dev is asynchronous on `stream`;
+ *    d_Pinv must not alias d_S.  _host is blocking. */
+#define GBDPCG_PINV_IDENTITY 0
+#define GBDPCG_PINV_JACOBI 1
+#define GBDPCG_PINV_STAIR 2
+GBDPCG_API int gbdpcg_build_pinv_dev_f32(gbdpcg_workspace *ws, const float *d_S, float *d_Pinv, uint32_t nx, uint32_t N, uint32_t batch,
+                                         int kind, void *stream);
+GBDPCG_API int gbdpcg_build_pinv_dev_f64(gbdpcg_workspace *ws, const double *d_S, double *d_Pinv, uint32_t nx, uint32_t N, uint32_t batch,
+                                         int kind, void *stream);
+GBDPCG_API int gbdpcg_build_pinv_host_f32(gbdpcg_workspace *ws, const float *h_S, float *h_Pinv, uint32_t nx, uint32_t N, uint32_t batch,
+                                          int kind);
+GBDPCG_API int gbdpcg_build_pinv_host_f64(gbdpcg_workspace *ws, const double *h_S, double *h_Pinv, uint32_t nx, uint32_t N, uint32_t batch,
+                                          int kind);
 
 /* -- launch-plan query: replaces pcgSharedMemSize<T> (reference include/pcg.cuh:13-20) and
  *    checkPcgOccupancy<T> (include/pcg.cuh:23-49) with what THIS library would launch. */

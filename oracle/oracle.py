@@ -40,6 +40,9 @@ def lib():
             h = getattr(_lib, f"oracle_bdmv_{suf}")
             h.restype = None
             h.argtypes = [C.c_void_p] * 3 + [C.c_uint32, C.c_uint32]
+            b = getattr(_lib, f"oracle_build_pinv_{suf}")
+            b.restype = C.c_int
+            b.argtypes = [C.c_void_p] * 2 + [C.c_uint32, C.c_uint32, C.c_int]
     return _lib
 
 
@@ -94,6 +97,21 @@ def pcg_batched(S, Pinv, gamma, lambda0, nx, N, exit_tol, max_iter, order=0, thr
     getattr(lib(), f"oracle_pcg_batched_{_suf(dt)}")(_ptr(S), _ptr(Pinv), _ptr(gamma), _ptr(lam), nx, N, B,
                                                      exit_tol, max_iter, order, _ptr(iters), _ptr(exits), threads)
     return lam, iters, exits.astype(bool)
+
+
+def build_pinv(S, nx, N, kind):
+    """Phi^-1 from S in the compressed layout; kind 0/1/2 or 'identity'/'jacobi'/'stair'
+    (restates glass::invertMatrix, reference GLASS/src/L3/inv.cuh:6-37, plus the stair products)."""
+    kind = {"identity": 0, "jacobi": 1, "stair": 2}.get(kind, kind)
+    S = np.ascontiguousarray(S)
+    P = np.empty_like(S)
+    per = 3 * N * nx * nx
+    Sf, Pf = S.reshape(-1, per), P.reshape(-1, per)
+    for i in range(Sf.shape[0]):
+        rc = getattr(lib(), f"oracle_build_pinv_{_suf(S.dtype)}")(_ptr(Sf[i]), _ptr(Pf[i]), nx, N, int(kind))
+        if rc != 0:
+            raise ValueError("oracle_build_pinv: bad arguments")
+    return P
 
 
 def pcg_numpy(S, Pinv, gamma, lambda0, nx, N, exit_tol, max_iter):

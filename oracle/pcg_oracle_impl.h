@@ -181,6 +181,86 @@ int FN(oracle_pcg_batched)(const T *S, const T *Pinv, const T *gamma, T *lambda,
     return 0;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * Preconditioner construction.  The reference never calls this, but it
+ * carries the primitive: glass::invertMatrix(dimA, A, s_temp), GLASS/src/L3/inv.cuh:6-37 --
+ * Gauss-Jordan on the augmented [V | I] (column-major, nx x 2nx) WITHOUT pivoting; per pivot p
+ * the window of columns p .. p+nx is updated: pivot row *= pvInv, every other row
+ * orv -= orpcv * pvInv * prvOld (left to right).  Restated literally; the inverse is the right
+ * half.  Formulae for the blocks: the paper cited at reference README.md:66-76 (not in the tree).
+ *   kind 0: Phi^-1 = I;  1: Phi^-1_kk = S_kk^-1;
+ *   2: additionally Phi^-1_{k,k+-1} = -(S_kk^-1 (S_{k,k+-1} S_{k+-1,k+-1}^-1))   (symmetric stair)
+ * Parity unpinned by the reference (no caller, no vectors): pinned by dense-inverse properties
+ * in tests/test_pinv_cpu.py (P_kk S_kk = I; stair blocks against numpy.linalg.inv in fp64).
+ * --------------------------------------------------------------------------------------------- */
+static void FN(invert_block)(const T *A, T *Ainv, uint32_t n, T *aug, T *s_temp)
+{
+    /* aug = [A | I], column-major, n rows x 2n columns */
+    for (uint32_t c = 0; c < n; c++)
+        for (uint32_t r = 0; r < n; r++) {
+            aug[(size_t)c * n + r] = A[(size_t)c * n + r];
+            aug[(size_t)(n + c) * n + r] = (r == c) ? (T)1 : (T)0;
+        }
+    for (uint32_t piv = 0; piv < n; piv++) {
+        size_t pco = (size_t)piv * n;
+        T pvInv = (T)1 / aug[piv + pco];
+        for (uint32_t ind = 0; ind < 2 * n + 1; ind++)               /* inv.cuh:18-23: pivot column, then pivot row */
+            s_temp[ind] = (ind < n) ? aug[ind + pco] : aug[piv + pco + (size_t)(ind - n) * n];
+        for (uint32_t ind = 0; ind < n * (n + 1); ind++) {           /* inv.cuh:26-31 */
+            uint32_t row = ind % n, col = ind / n;
+            size_t at = row + pco + (size_t)col * n;
+            if (row == piv) aug[at] *= pvInv;
+            else aug[at] -= s_temp[row] * pvInv * s_temp[n + col];
+        }
+    }
+    for (uint32_t e = 0; e < n * n; e++) Ainv[e] = aug[(size_t)n * n + e];
+}
+
+/* C = A B, all n x n column-major, inner index ascending */
+static void FN(block_mm)(const T *A, const T *B, T *Cm, uint32_t n)
+{
+    for (uint32_t c = 0; c < n; c++)
+        for (uint32_t r = 0; r < n; r++) {
+            T acc = (T)0;
+            for (uint32_t q = 0; q < n; q++) acc += A[(size_t)q * n + r] * B[(size_t)c * n + q];
+            Cm[(size_t)c * n + r] = acc;
+        }
+}
+
+int FN(oracle_build_pinv)(const T *S, T *P, uint32_t nx, uint32_t N, int kind)
+{
+    if (!S || !P || nx == 0 || N < 2 || kind < 0 || kind > 2) return -1;
+    size_t bb = (size_t)nx * nx, bsz = 3 * bb;
+    T *dinv = (T *)malloc(sizeof(T) * bb * N);
+    T *aug = (T *)malloc(sizeof(T) * 2 * bb + sizeof(T) * nx);
+    T *tmp = (T *)malloc(sizeof(T) * 2 * bb);
+    T *s_temp = (T *)malloc(sizeof(T) * (2 * nx + 1));
+    if (!dinv || !aug || !tmp || !s_temp) { free(dinv); free(aug); free(tmp); free(s_temp); return -2; }
+    memset(P, 0, sizeof(T) * bsz * N);
+    for (uint32_t k = 0; k < N; k++) {
+        if (kind == 0) {
+            for (uint32_t r = 0; r < nx; r++) P[k * bsz + bb + (size_t)r * nx + r] = (T)1;
+        } else {
+            FN(invert_block)(S + k * bsz + bb, dinv + k * bb, nx, aug, s_temp);
+            memcpy(P + k * bsz + bb, dinv + k * bb, sizeof(T) * bb);
+        }
+    }
+    if (kind == 2) {
+        for (uint32_t k = 0; k < N; k++)
+            for (int side = 0; side < 2; side++) {
+                if ((side == 0 && k == 0) || (side == 1 && k == N - 1)) continue;
+                uint32_t kn = side ? k + 1 : k - 1;
+                const T *So = S + k * bsz + (side ? 2 * bb : 0);
+                T *dst = P + k * bsz + (side ? 2 * bb : 0);
+                FN(block_mm)(So, dinv + kn * bb, tmp, nx);
+                FN(block_mm)(dinv + k * bb, tmp, tmp + bb, nx);
+                for (size_t e = 0; e < bb; e++) dst[e] = -tmp[bb + e];
+            }
+    }
+    free(dinv); free(aug); free(tmp); free(s_temp);
+    return 0;
+}
+
 #undef FN
 #undef CAT
 #undef CAT_

@@ -1,0 +1,4 @@
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_pinv_gpu.py -q -x --timeout=180 > gpurun_out/s10b_pytest.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/s10b_pytest.log
+timeout 300 python scripts/time_pinv.py 2>&1 | tee gpurun_out/s10b_time_pinv.log | tail -12
+timeout 300 python -m pytest tests -m gpu -q -x > gpurun_out/s10b_memcheck.log 2>&1; echo "memcheck rc=$?"; tail -5 gpurun_out/s10b_memcheck.log
