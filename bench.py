@@ -8,8 +8,9 @@ A "step" is one pass of the hot path over one batch: 8192 independent iiwa-sized
 per GPU (weak scaling: every rank owns its own 8192 problems, no collective on the data path).
 
   value      whole-job solves/s with inputs resident in HBM, CUDA events around each launch, max over ranks
-  e2e        same metric through the host-pointer C ABI (gbdpcg_solve_batched_host_f32): pinned host buffers,
-             H2D + solve + D2H inside the timed region
+  e2e        same metric through the host-pointer C ABI (gbdpcg_solve_batched_host_f32) with the reference's host
+             signature (S, gamma, lambda; Phi^-1 formed on the device): pinned host buffers, H2D + build + solve + D2H
+             inside the timed region; the variant that also ships Phi^-1 from the host is reported beside it
   roofline   HBM roofline of the batched kernel (algorithmic bytes / launch time vs MEASURED_PEAKS.json)
   single_solve   p50/p99 latency of ONE C2 solve (the north-star latency target) in three scopes
   cpu_baseline   the host oracle (oracle/, test infrastructure) on the box's cores, bounded sample
@@ -221,23 +222,50 @@ def run_ours(args):
     hg, pg = pinned_array(lib, gam.shape, DTYPE); hg[:] = gam
     hl, pl = pinned_array(lib, gam.shape, DTYPE)
     e2e_steps = max(2, min(args.steps, 5))
-    for _ in range(2):
-        hl[:] = 0
-        g.solve_batched_host(hS, hP, hg, hl, NX, N_KNOT, batch, cfg)
-    barrier()
-    t_e2e = 0.0
-    for _ in range(e2e_steps):
-        hl[:] = 0
-        t0 = time.perf_counter()
-        e_it, e_ex = g.solve_batched_host(hS, hP, hg, hl, NX, N_KNOT, batch, cfg)
-        t_e2e += time.perf_counter() - t0
-    e2e_t = torch.tensor([t_e2e / e2e_steps], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_value = batch * world / float(e2e_t.item())
-    assert np.array_equal(e_it, iters.astype(np.uint32)), "host path and device path disagree"
-    h2d = (S.nbytes + P.nbytes + gam.nbytes + hl.nbytes)
+
+    def time_host_path(h_P, cfg_h):
+        for _ in range(2):
+            hl[:] = 0
+            g.solve_batched_host(hS, h_P, hg, hl, NX, N_KNOT, batch, cfg_h)
+        barrier()
+        t = 0.0
+        for _ in range(e2e_steps):
+            hl[:] = 0
+            t0 = time.perf_counter()
+            its, _ = g.solve_batched_host(hS, h_P, hg, hl, NX, N_KNOT, batch, cfg_h)
+            t += time.perf_counter() - t0
+        tt = torch.tensor([t / e2e_steps], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return batch * world / float(tt.item()), its
+
+    # (a) the reference's own host signature: S, gamma, lambda only (include/interface.cuh:24-31 has no Pinv parameter);
+    #     the symmetric-stair Phi^-1 is formed from S on the device (GBDPCG_FLAG_BUILD_STAIR) -- the headline e2e
+    cfg_build = g.pcg_config(pcg_exit_tol=TOL, pcg_max_iter=MAX_ITER, flags=_lib.FLAG_BUILD_STAIR)
+    e2e_value, e_it = time_host_path(None, cfg_build)
+    lam_build = hl.copy()
+    assert int(np.abs(e_it.astype(np.int64) - iters.astype(np.int64)).max()) <= 1, "device-built preconditioner changed iteration counts"
+    h2d = (S.nbytes + gam.nbytes + hl.nbytes)
     d2h = (hl.nbytes + 4 * batch + batch)
+    # (b) same call with Phi^-1 handed over by the host (twice the PCIe bytes)
+    e2e_hostp, e_it2 = time_host_path(hP, cfg)
+    assert np.array_equal(e_it2, iters.astype(np.uint32)), "host path and device path disagree"
+    lam_err = float(np.abs(lam_build - hl).max() / np.abs(hl).max())
+
+    # ---- device-resident preconditioner build (events) ----
+    d_Pb = torch.empty_like(d_S)
+    for _ in range(3):
+        g.build_pinv_dev(NX, N_KNOT, batch, d_S, d_Pb, "stair")
+    barrier()
+    evb = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(10)]
+    for a, b in evb:
+        a.record()
+        g.build_pinv_dev(NX, N_KNOT, batch, d_S, d_Pb, "stair")
+        b.record()
+    barrier()
+    build_ms = statistics.median(a.elapsed_time(b) for a, b in evb)
+    build_err = float((d_Pb - d_P).abs().max().item() / d_P.abs().max().item())
+    del d_Pb
     for p in (pS, pP, pg, pl):
         lib.gbdpcg_host_free(p)
 
@@ -291,6 +319,11 @@ def run_ours(args):
             g.pcg_solve(hS1, hg1, hl1, NX, N_KNOT, cfg, h_Pinv=hP1)
         lat_h = time_blocking_calls(host_call)
 
+        def host_call_build():
+            hl1[:] = 0
+            g.pcg_solve(hS1, hg1, hl1, NX, N_KNOT, cfg_build)
+        lat_hb = time_blocking_calls(host_call_build)
+
         # ---- CPU baseline: host oracle on a bounded sample, all cores ----
         from oracle import oracle
         cores = os.cpu_count() or 1
@@ -316,7 +349,12 @@ def run_ours(args):
             "pcg_iters": {"min": int(iters.min()), "mean": float(iters.mean()), "max": int(iters.max())},
             "iterations_per_s": float(iters.mean()) * value,
             "e2e": {"value": e2e_value, "unit": "solves/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "steps": e2e_steps, "api": "gbdpcg_solve_batched_host_f32 (pinned host buffers, chunked 2-stream overlap)"},
+                    "steps": e2e_steps, "api": "gbdpcg_solve_batched_host_f32(S, gamma, lambda) with GBDPCG_FLAG_BUILD_STAIR: the "
+                    "reference's host signature (no Pinv argument), Phi^-1 formed on the device; pinned host buffers, chunked "
+                    "2-stream overlap", "with_host_pinv": {"value": e2e_hostp, "h2d_bytes_per_step": int(h2d + P.nbytes)},
+                    "lambda_max_diff_vs_host_pinv": lam_err},
+            "pinv_build": {"ms": build_ms, "gb_per_s": 2 * S.nbytes / build_ms / 1e6, "max_rel_diff_vs_fp64_host_build": build_err,
+                           "note": "gbdpcg_build_pinv_dev_f32 (stair) on the resident batch: reads S, writes Phi^-1"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(batch), "algorithmic_bytes_per_launch": bytes_per_solve * batch,
@@ -329,7 +367,8 @@ def run_ours(args):
                              "kernel_p50_us": pct(lat_k, 0.5), "kernel_p99_us": pct(lat_k, 0.99),
                              "iterations_per_s": it1 / (pct(lat_k, 0.5) * 1e-6),
                              "dev_api_p50_us": pct(lat_d, 0.5), "dev_api_p99_us": pct(lat_d, 0.99),
-                             "host_api_p50_us": pct(lat_h, 0.5), "host_api_p99_us": pct(lat_h, 0.99)},
+                             "host_api_p50_us": pct(lat_h, 0.5), "host_api_p99_us": pct(lat_h, 0.99),
+                             "host_api_device_built_pinv_p50_us": pct(lat_hb, 0.5), "host_api_device_built_pinv_p99_us": pct(lat_hb, 0.99)},
             "cpu_baseline": {"value": ns / t_cpu, "unit": "solves/s", "cores": cores, "kind": "port",
                              "sample": f"{ns} of the {batch} systems, host oracle (oracle/pcg_oracle.c), {cores} threads",
                              "single_thread_solve_us": t_cpu1 * 1e6, "iters_mean": float(it_c.mean())},

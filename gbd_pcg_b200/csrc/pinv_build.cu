@@ -47,6 +47,7 @@ int launch_pinv_build(const T *d_S, T *d_Pinv, uint32_t nx, uint32_t N, uint32_t
 {
     PinvArgs a;
     a.S = d_S; a.P = d_Pinv; a.mat_stride = 3ull * N * nx * nx; a.N = N; a.batch = batch; a.kind = kind;
+    a.use_tma = ((uintptr_t)d_S % 16 == 0 && (uintptr_t)d_Pinv % 16 == 0 && (3ull * nx * nx * sizeof(T)) % 16 == 0) ? 1 : 0;
     int sms = 148, dev = 0;
     if (!plan_only) {
         cudaError_t e = cudaGetDevice(&dev);

@@ -10,7 +10,7 @@
 //                       Phi^-1_{k,k-1} = -S_kk^-1 S_{k,k-1} S_{k-1,k-1}^-1   (left block of block-row k)
 // Output is in the compressed block-tridiagonal layout of the solver (include/pcg.cuh:104-110); padding blocks are zero.
 //
-// Mapping: ONE THREAD PER BLOCK COLUMN.  A group of NX lanes owns one nx x nx block; lane j keeps column j in registers.
+// Mapping: a group of nx/CPL lanes owns one nx x nx block; a lane keeps CPL (= 2) columns of it in registers.
 //   * inversion: in-place Gauss-Jordan in the reference's arithmetic order (row p scaled by 1/pivot, every other row
 //     r updated as a[r] -= (col_p[r] * pvInv) * a[p], inv.cuh:27-33); the pivot column is broadcast through a
 //     16-float shared scratch line per group, __syncwarp only.
@@ -33,7 +33,44 @@ struct PinvArgs {
     unsigned long long mat_stride;   // elements between consecutive problems
     uint32_t N, batch, chunk, nchunks;
     int kind;
+    int use_tma;                     // host decided: S, P and the problem stride are 16-byte aligned
 };
+
+// ---- TMA engine (1-D bulk copies) + mbarrier, used for the chunk image in both directions ----
+__device__ __forceinline__ uint32_t pv_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pv_mbar_init(uint32_t mbar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void pv_mbar_expect_tx(uint32_t mbar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void pv_mbar_wait(uint32_t mbar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "PV_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra PV_DONE_%=;\n"
+        "bra PV_WAIT_%=;\n"
+        "PV_DONE_%=:\n"
+        "}\n" ::"r"(mbar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void pv_bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t mbar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(mbar) : "memory");
+}
+__device__ __forceinline__ void pv_bulk_s2g(void *dst, uint32_t src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void pv_bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void pv_fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 template <typename T> struct PVec;
 template <> struct PVec<float> { typedef float4 type; static constexpr int V = 4; };
@@ -45,13 +82,16 @@ template <typename T, int V> __device__ __forceinline__ void unpack_vec(const ty
     else { x[0] = q.x; x[1] = q.y; x[2] = (T)0; x[3] = (T)0; }
 }
 
-// y = M v for a column-major NX x NX block in shared memory (flat 16-byte loads shared by the whole group)
-template <typename T, int NX>
-__device__ __forceinline__ void block_mv_bcast(const T *__restrict__ M, const T (&v)[NX], T (&y)[NX])
+// Y = M V for a column-major NX x NX block M in shared memory and C columns V held by the lane (flat 16-byte loads
+// shared by the whole group; every element of M that reaches a register is used for C multiply-adds)
+template <typename T, int NX, int C>
+__device__ __forceinline__ void block_mv_bcast(const T *__restrict__ M, const T (&v)[C][NX], T (&y)[C][NX])
 {
     constexpr int V = PVec<T>::V;
 #pragma unroll
-    for (int r = 0; r < NX; r++) y[r] = (T)0;
+    for (int c = 0; c < C; c++)
+#pragma unroll
+        for (int r = 0; r < NX; r++) y[c][r] = (T)0;
     if constexpr ((NX * NX) % V == 0) {
 #pragma unroll
         for (int e = 0; e < NX * NX; e += V) {
@@ -59,11 +99,15 @@ __device__ __forceinline__ void block_mv_bcast(const T *__restrict__ M, const T 
             T x[4];
             unpack_vec<T, V>(q, x);
 #pragma unroll
-            for (int u = 0; u < V; u++) y[(e + u) % NX] += x[u] * v[(e + u) / NX];
+            for (int u = 0; u < V; u++)
+#pragma unroll
+                for (int c = 0; c < C; c++) y[c][(e + u) % NX] += x[u] * v[c][(e + u) / NX];
         }
     } else {
 #pragma unroll
-        for (int e = 0; e < NX * NX; e++) y[e % NX] += M[e] * v[e / NX];
+        for (int e = 0; e < NX * NX; e++)
+#pragma unroll
+            for (int c = 0; c < C; c++) y[c][e % NX] += M[e] * v[c][e / NX];
     }
 }
 
@@ -97,26 +141,22 @@ __host__ __device__ inline size_t pinv_smem_bytes(int nx, int chunk, int threads
 {
     const int groups = (threads / 32) * (32 / (nx / pinv_cpl(nx)));
     size_t e = (size_t)chunk * 3 * nx * nx + (size_t)(chunk + 2) * nx * nx + (size_t)groups * 16;
-    return e * sizeof(T) + 32;
+    return e * sizeof(T) + 48;       // + mbarrier slot in front
 }
 
 template <typename T, int NX>
 __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
 {
     constexpr int BB = NX * NX, BSZ = 3 * BB;
-    constexpr int GPW = 32 / NX;                    // groups (blocks in flight) per warp
     extern __shared__ __align__(16) unsigned char pinv_smem_raw[];
-    T *img = reinterpret_cast<T *>(pinv_smem_raw);
+    const uint32_t mbar = pv_smem_u32(pinv_smem_raw);
+    T *img = reinterpret_cast<T *>(pinv_smem_raw + 16);
     const int chunk = (int)a.chunk, N = (int)a.N;
     T *dinv = img + (size_t)chunk * BSZ;
     T *scr_all = dinv + (size_t)(chunk + 2) * BB;
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
-    const int gl = lane / NX, j = lane - gl * NX;   // group inside the warp, column owned inside the block
-    const bool lane_on = gl < GPW;
-    const int group = warp * GPW + gl;
-    const int ngroups = (blockDim.x >> 5) * GPW;
-    // phase 1 mapping: CPL columns per lane
+    // lane mapping: LPB lanes per block, CPL columns of it per lane
     constexpr int CPL = pinv_cpl(NX), LPB = NX / CPL, GPW1 = 32 / LPB;
     const int gl1 = lane / LPB, li = lane - gl1 * LPB;
     const bool lane_on1 = gl1 < GPW1;
@@ -127,6 +167,10 @@ __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
     const T *Sg = static_cast<const T *>(a.S);
     T *Pg = static_cast<T *>(a.P);
     const uint32_t items = a.batch * a.nchunks;
+    const bool tma = a.use_tma != 0;
+    uint32_t phase = 0;
+    if (tma && t == 0) pv_mbar_init(mbar, 1);
+    __syncthreads();
 
     for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
         const uint32_t prob = item / a.nchunks;
@@ -141,8 +185,21 @@ __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
                 img[e] = (c == NX + r) ? (T)1 : (T)0;
             }
         } else {
-            copy_coalesced<T>(img, Sp + (size_t)k0 * BSZ, cnt * BSZ, true);
-            __syncthreads();
+            if (tma) {
+                // one thread: the previous item's bulk store must have finished READING the image, then the TMA engine
+                // fetches this item's chunk of S; everybody waits on the mbarrier
+                if (t == 0) {
+                    pv_bulk_wait_read();
+                    const uint32_t bytes = (uint32_t)(cnt * BSZ * (int)sizeof(T));
+                    pv_mbar_expect_tx(mbar, bytes);
+                    pv_bulk_g2s(pv_smem_u32(img), Sp + (size_t)k0 * BSZ, bytes, mbar);
+                }
+                pv_mbar_wait(mbar, phase);
+                phase ^= 1;
+            } else {
+                copy_coalesced<T>(img, Sp + (size_t)k0 * BSZ, cnt * BSZ, true);
+                __syncthreads();
+            }
 
             // ---- phase 1: D_k^-1 for k = k0-1 .. k0+cnt (halo blocks come straight from global memory) ----
             // CPL columns per lane, LPB lanes per block.  Per pivot p the owner of column p publishes the scaled pivot
@@ -212,39 +269,56 @@ __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
             }
             __syncthreads();
 
-            // ---- phase 2: off-diagonal blocks, rewritten in place ----
+            // ---- phase 2: off-diagonal blocks, rewritten in place (same lane mapping: CPL columns per lane) ----
             const int ntask = 2 * cnt;
-            for (int base = 0; base < ntask; base += ngroups) {
-                const int i = base + group;
-                const bool valid = lane_on && i < ntask;
+            for (int base = 0; base < ntask; base += ngroups1) {
+                const int i = base + group1;
+                const bool valid = lane_on1 && i < ntask;
                 const int lb = valid ? (i >> 1) : 0, side = i & 1;       // side 0: left block (k, k-1); 1: right block (k, k+1)
                 const int k = k0 + lb, kn = side ? k + 1 : k - 1;
                 const bool real = valid && a.kind == PINV_STAIR && kn >= 0 && kn < N;
                 T *blk = img + (size_t)lb * BSZ + (side ? 2 * BB : 0);
-                T out[NX];
+                T out[CPL][NX];
 #pragma unroll
-                for (int r = 0; r < NX; r++) out[r] = (T)0;
+                for (int c = 0; c < CPL; c++)
+#pragma unroll
+                    for (int r = 0; r < NX; r++) out[c][r] = (T)0;
                 if (real) {
-                    T v[NX], w[NX];
-                    const T *dn = dinv + (size_t)(kn - k0 + 1) * BB + j * NX;
+                    T v[CPL][NX], w[CPL][NX];
+                    const T *dn = dinv + (size_t)(kn - k0 + 1) * BB + li * CPL * NX;
 #pragma unroll
-                    for (int r = 0; r < NX; r++) v[r] = dn[r];
-                    block_mv_bcast<T, NX>(blk, v, w);                              // w = S_off (D_kn^-1)[:, j]
-                    block_mv_bcast<T, NX>(dinv + (size_t)(lb + 1) * BB, w, out);   // out = D_k^-1 w
+                    for (int c = 0; c < CPL; c++)
 #pragma unroll
-                    for (int r = 0; r < NX; r++) out[r] = -out[r];
+                        for (int r = 0; r < NX; r++) v[c][r] = dn[c * NX + r];
+                    block_mv_bcast<T, NX, CPL>(blk, v, w);                              // w = S_off (D_kn^-1)[:, cols]
+                    block_mv_bcast<T, NX, CPL>(dinv + (size_t)(lb + 1) * BB, w, out);   // out = D_k^-1 w
+#pragma unroll
+                    for (int c = 0; c < CPL; c++)
+#pragma unroll
+                        for (int r = 0; r < NX; r++) out[c][r] = -out[c][r];
                 }
                 __syncwarp();      // every lane of the group has finished reading S_off before it is overwritten
                 if (valid) {
 #pragma unroll
-                    for (int r = 0; r < NX; r++) blk[j * NX + r] = out[r];
+                    for (int c = 0; c < CPL; c++)
+#pragma unroll
+                        for (int r = 0; r < NX; r++) blk[(li * CPL + c) * NX + r] = out[c][r];
                 }
             }
         }
-        __syncthreads();
-        copy_coalesced<T>(Pp + (size_t)k0 * BSZ, img, cnt * BSZ, false);
-        __syncthreads();
+        if (tma) {
+            pv_fence_async();          // generic-proxy writes of the image become visible to the TMA engine
+            __syncthreads();
+            if (t == 0) pv_bulk_s2g(Pp + (size_t)k0 * BSZ, pv_smem_u32(img), (uint32_t)(cnt * BSZ * (int)sizeof(T)));
+            // the image is not touched again before thread 0 has waited for the store to finish reading it (loop top)
+            if (a.kind == PINV_IDENTITY) { if (t == 0) pv_bulk_wait_read(); __syncthreads(); }
+        } else {
+            __syncthreads();
+            copy_coalesced<T>(Pp + (size_t)k0 * BSZ, img, cnt * BSZ, false);
+            __syncthreads();
+        }
     }
+    if (tma && t == 0) pv_bulk_wait_read();   // shared memory must outlive the last bulk store
 }
 
 // Runtime-nx fallback (odd or large state sizes): one CTA per (problem, block-row); cooperative in-place Gauss-Jordan of
