@@ -36,12 +36,34 @@ class pcg_config:
     pcg_grid: tuple = DEFAULT_GRID
     pcg_block: tuple = DEFAULT_BLOCK
     empty_pinv: int = 1
-    # extensions (not in the reference): launch tuning knobs of the C ABI
+    # extensions (not in the reference): what the host overload without a Phi^-1 argument builds on the device when
+    # empty_pinv == 0 ("stair" | "jacobi" | "identity"), and the launch tuning knobs of the C ABI
+    pinv_build: str = field(default="stair", repr=False)
     flags: int = field(default=0, repr=False)
     cluster: int = field(default=0, repr=False)
 
     def to_c(self) -> Config:
         return Config(float(self.pcg_exit_tol), int(self.pcg_max_iter), int(self.empty_pinv), int(self.flags), int(self.cluster))
+
+
+@dataclass
+class csr_t:
+    """Mirror of reference ``csr_t<T>`` (include/types.cuh:7-15): uint32 row_ptr[rows+1], col_ind[nnz], T val[nnz]."""
+    row_ptr: np.ndarray
+    col_ind: np.ndarray
+    val: np.ndarray
+    rows: int
+    cols: int
+    nnz: int
+
+    @staticmethod
+    def from_dense(A, dtype=None, keep_zeros=False):
+        A = np.asarray(A)
+        mask = np.ones_like(A, dtype=bool) if keep_zeros else (A != 0)
+        counts = mask.sum(axis=1)
+        row_ptr = np.concatenate([[0], np.cumsum(counts)]).astype(np.uint32)
+        rr, cc = np.nonzero(mask)
+        return csr_t(row_ptr, cc.astype(np.uint32), np.ascontiguousarray(A[rr, cc], dtype=dtype or A.dtype), A.shape[0], A.shape[1], int(rr.size))
 
 
 def _suffix(dtype) -> str:
@@ -98,6 +120,8 @@ def _stream_ptr(stream):
 # ------------------------------------------------------------------------------------------------
 def solvePCG(*args, **kw):
     """Both reference overloads, selected like C++ would: 6 arguments = host pointers, 11 = device pointers."""
+    if args and isinstance(args[0], csr_t):
+        return _solve_csr(*args, **kw)
     if args and isinstance(args[0], np.ndarray):
         return _solve_host(*args, **kw)
     if args and isinstance(args[0], (int, np.integer)):
@@ -113,18 +137,20 @@ def pcg_solve(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv
 def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None, return_flag=False):
     """Host-pointer overload.  ``h_lambda`` is updated in place; returns the iteration count
     (the reference returns 1 unconditionally, include/interface.cuh:88 -- a defect this build does not keep).
-    ``h_Pinv`` (extension) supplies Phi^-1; it is used only when ``config.empty_pinv == 0``."""
+    ``h_Pinv`` (extension) supplies Phi^-1; it is used only when ``config.empty_pinv == 0``.  Without it,
+    ``empty_pinv == 0`` makes the library form ``config.pinv_build`` from S on the device."""
     config = config or pcg_config()
-    builds = bool(config.flags & (_lib.FLAG_BUILD_JACOBI | _lib.FLAG_BUILD_STAIR))
-    if not config.empty_pinv and h_Pinv is None and not builds:
-        # the reference prints this and carries on with an uninitialised d_Pinv (interface.cuh:33-34,45-46)
-        print("This api can only be called with no preconditioner")
     suf = _suffix(h_S.dtype)
     nx, N = int(stateSize), int(knotPoints)
     ms, vs = 3 * N * nx * nx, N * nx
     cfg = config.to_c()
     if h_Pinv is None:
-        cfg.empty_pinv = 1
+        if not config.empty_pinv and config.pinv_build in BUILD_FLAGS:
+            # no Phi^-1 argument (the reference's own signature): it is formed from S on the device.  The reference
+            # prints a warning here and solves with an uninitialised d_Pinv (interface.cuh:33-34,45-46).
+            cfg.flags |= BUILD_FLAGS[config.pinv_build]
+        elif not (cfg.flags & (_lib.FLAG_BUILD_JACOBI | _lib.FLAG_BUILD_STAIR)):
+            cfg.empty_pinv = 1
     it, ex = C.c_uint32(0), C.c_int32(0)
     f = getattr(_lib.lib(), f"gbdpcg_solve_host_{suf}")
     _lib.check(f(None, _host(h_S, h_S.dtype, ms, "h_S"),
@@ -132,6 +158,49 @@ def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pi
                  _host(h_gamma, h_S.dtype, vs, "h_gamma"), _host(h_lambda, h_S.dtype, vs, "h_lambda", True),
                  nx, N, C.byref(cfg), C.byref(it), C.byref(ex)))
     return (it.value, bool(ex.value)) if return_flag else it.value
+
+
+def _solve_csr(h_S, h_Pinv, h_gamma, h_lambda, stateSize, knotPoints, config=None, return_flag=False):
+    """CSR overload (reference include/interface.cuh:8-20 is a stub: "NOT IMPLEMENTED", exit 12).  ``h_S`` / ``h_Pinv`` are
+    ``csr_t``; ``h_Pinv`` may be None (then ``config.empty_pinv == 0`` forms ``config.pinv_build`` on the device)."""
+    config = config or pcg_config()
+    dt = h_S.val.dtype
+    suf = _suffix(dt)
+    nx, N = int(stateSize), int(knotPoints)
+    if h_S.rows != nx * N or h_S.cols != nx * N:
+        raise ValueError("CSR S must be square with stateSize*knotPoints rows")
+    cfg = config.to_c()
+    if h_Pinv is None:
+        if not config.empty_pinv and config.pinv_build in BUILD_FLAGS:
+            cfg.flags |= BUILD_FLAGS[config.pinv_build]
+        elif not (cfg.flags & (_lib.FLAG_BUILD_JACOBI | _lib.FLAG_BUILD_STAIR)):
+            cfg.empty_pinv = 1
+
+    def arrs(m):
+        if m is None:
+            return [None, None, None, 0]
+        rp = np.ascontiguousarray(m.row_ptr, dtype=np.uint32)
+        ci = np.ascontiguousarray(m.col_ind, dtype=np.uint32)
+        v = np.ascontiguousarray(m.val, dtype=dt)
+        if rp.size != m.rows + 1 or ci.size < m.nnz or v.size < m.nnz:
+            raise ValueError("inconsistent CSR arrays")
+        keep.extend([rp, ci, v])
+        return [rp.ctypes.data_as(C.c_void_p), ci.ctypes.data_as(C.c_void_p), v.ctypes.data_as(C.c_void_p), int(m.nnz)]
+    keep = []
+    it, ex = C.c_uint32(0), C.c_int32(0)
+    f = getattr(_lib.lib(), f"gbdpcg_solve_csr_host_{suf}")
+    _lib.check(f(None, *arrs(h_S), *arrs(h_Pinv), _host(h_gamma, dt, nx * N, "h_gamma"), _host(h_lambda, dt, nx * N, "h_lambda", True),
+                 nx, N, C.byref(cfg), C.byref(it), C.byref(ex)))
+    return (it.value, bool(ex.value)) if return_flag else it.value
+
+
+def pack_csr_dev(d_row_ptr, d_col_ind, d_val, rows, state_size, knot_points, d_out, d_status=None, stream=None):
+    """Device CSR -> compressed block-tridiagonal layout (asynchronous).  ``d_status`` (int32[1]) gets bit 0 set when an
+    entry lies outside the band."""
+    suf = _torch_dtype_suffix(d_val)
+    f = getattr(_lib.lib(), f"gbdpcg_pack_csr_dev_{suf}")
+    _lib.check(f(None, _dev_ptr(d_row_ptr, "d_row_ptr"), _dev_ptr(d_col_ind, "d_col_ind"), _dev_ptr(d_val, "d_val"), int(rows),
+                 int(state_size), int(knot_points), _dev_ptr(d_out, "d_out"), _dev_ptr(d_status, "d_status", True), _stream_ptr(stream)))
 
 
 def _solve_dev(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_r=None, d_p=None, d_v_temp=None,

@@ -18,6 +18,7 @@
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
 #include "pinv_build.h"
+#include "csr_pack.cuh"
 
 namespace gbdpcg {
 
@@ -320,8 +321,8 @@ struct gbdpcg_workspace {
     int device = -1;
     std::mutex mu;
     cudaStream_t streams[2] = {nullptr, nullptr};
-    void *dbuf[4] = {nullptr, nullptr, nullptr, nullptr};  // S, Pinv, gamma, lambda
-    size_t dcap[4] = {0, 0, 0, 0};
+    void *dbuf[8] = {};    // S, Pinv, gamma, lambda, then CSR staging: row_ptr, col_ind, val, status
+    size_t dcap[8] = {};
     uint32_t *d_iters = nullptr;
     uint8_t *d_exits = nullptr;
     size_t cap_batch = 0;
@@ -577,6 +578,83 @@ static int build_pinv_host(gbdpcg_workspace *user_ws, const T *hS, T *hP, uint32
     return GBDPCG_OK;
 }
 
+// ---- CSR front end (reference include/interface.cuh:8-20 is a stub) ----
+template <typename T>
+static int pack_csr_dev(const uint32_t *row_ptr, const uint32_t *col_ind, const T *val, uint32_t rows, uint32_t nx, uint32_t N,
+                        T *out, int32_t *d_status, cudaStream_t st)
+{
+    if (!row_ptr || !col_ind || !val || !out) return fail(GBDPCG_ERR_INVALID, "CSR arrays and the output must not be NULL");
+    if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
+    if ((uint64_t)rows != (uint64_t)nx * N) return fail(GBDPCG_ERR_INVALID, "CSR matrix has %u rows, expected stateSize*knotPoints = %llu", rows,
+                                                        (unsigned long long)nx * N);
+    CK(cudaMemsetAsync(out, 0, sizeof(T) * 3 * (size_t)N * nx * nx, st));
+    if (d_status) CK(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
+    const uint32_t blocks = (rows + 7) / 8 < 1184 ? (rows + 7) / 8 : 1184;       // one warp per row, at most 8 CTAs per SM
+    csr_pack_kernel<T><<<blocks, 256, 0, st>>>(row_ptr, col_ind, val, rows, nx, N, out, d_status);
+    CK(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
+struct HostCsr { const uint32_t *row_ptr, *col_ind; const void *val; uint32_t nnz; };
+
+template <typename T>
+static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const T *hg, T *hl, uint32_t nx, uint32_t N,
+                          const gbdpcg_config *cfg, uint32_t *iters, int32_t *max_iter_exit)
+{
+    int rc = check_args(S.val, hg, hl, nx, N, cfg);
+    if (rc) return rc;
+    if (!S.row_ptr || !S.col_ind) return fail(GBDPCG_ERR_INVALID, "S.row_ptr and S.col_ind must not be NULL");
+    gbdpcg_workspace *w;
+    if ((rc = get_ws(user_ws, &w))) return rc;
+    std::lock_guard<std::mutex> lk(w->mu);
+    const int bk = build_kind(cfg);
+    const bool csr_p = P.val && P.row_ptr && P.col_ind && cfg->empty_pinv == 0 && bk < 0;
+    const bool has_p = bk >= 0 || csr_p;
+    const uint32_t rows = nx * N;
+    const size_t mb = sizeof(T) * 3 * (size_t)N * nx * nx, vb = sizeof(T) * (size_t)N * nx;
+    const uint32_t max_nnz = (csr_p && P.nnz > S.nnz) ? P.nnz : S.nnz;
+    if ((rc = ws_reserve(w, 0, mb))) return rc;
+    if (has_p && (rc = ws_reserve(w, 1, mb))) return rc;
+    if ((rc = ws_reserve(w, 2, vb))) return rc;
+    if ((rc = ws_reserve(w, 3, vb))) return rc;
+    if ((rc = ws_reserve(w, 4, sizeof(uint32_t) * ((size_t)rows + 1)))) return rc;
+    if ((rc = ws_reserve(w, 5, sizeof(uint32_t) * (size_t)(max_nnz ? max_nnz : 1)))) return rc;
+    if ((rc = ws_reserve(w, 6, sizeof(T) * (size_t)(max_nnz ? max_nnz : 1)))) return rc;
+    if ((rc = ws_reserve(w, 7, 2 * sizeof(int32_t)))) return rc;
+    cudaStream_t st = w->streams[0];
+    int32_t *d_status = (int32_t *)w->dbuf[7];
+    auto upload_and_pack = [&](const HostCsr &M, T *dst, int32_t *stat) -> int {
+        CK(cudaMemcpyAsync(w->dbuf[4], M.row_ptr, sizeof(uint32_t) * ((size_t)rows + 1), cudaMemcpyHostToDevice, st));
+        if (M.nnz) {
+            CK(cudaMemcpyAsync(w->dbuf[5], M.col_ind, sizeof(uint32_t) * (size_t)M.nnz, cudaMemcpyHostToDevice, st));
+            CK(cudaMemcpyAsync(w->dbuf[6], M.val, sizeof(T) * (size_t)M.nnz, cudaMemcpyHostToDevice, st));
+        }
+        return pack_csr_dev<T>((const uint32_t *)w->dbuf[4], (const uint32_t *)w->dbuf[5], (const T *)w->dbuf[6], rows, nx, N, dst, stat, st);
+    };
+    if ((rc = upload_and_pack(S, (T *)w->dbuf[0], d_status))) return rc;
+    if (csr_p) { if ((rc = upload_and_pack(P, (T *)w->dbuf[1], d_status + 1))) return rc; }
+    else if (bk >= 0) { if ((rc = build_pinv_dev<T>((const T *)w->dbuf[0], (T *)w->dbuf[1], nx, N, 1, bk, st))) return rc; }
+    // the band check must pass before the solve is worth running
+    int32_t h_status[2] = {0, 0};
+    CK(cudaMemcpyAsync(h_status, d_status, (csr_p ? 2 : 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(w->dbuf[2], hg, vb, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(w->dbuf[3], hl, vb, cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    if (h_status[0] || h_status[1])
+        return fail(GBDPCG_ERR_INVALID, "%s has entries outside the block-tridiagonal band of block size %u", h_status[0] ? "S" : "Pinv", nx);
+    gbdpcg_config c1 = *cfg;
+    c1.empty_pinv = has_p ? 0 : 1;
+    rc = solve_batched_dev<T>((const T *)w->dbuf[0], has_p ? (const T *)w->dbuf[1] : nullptr, (const T *)w->dbuf[2], (T *)w->dbuf[3],
+                              nx, N, 1, &c1, w->hd_iters, w->hd_exit, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(hl, w->dbuf[3], vb, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (iters) *iters = *(volatile uint32_t *)w->h_iters;
+    if (max_iter_exit) *max_iter_exit = *(volatile uint8_t *)w->h_exit;
+    return GBDPCG_OK;
+}
+
 template <typename T>
 static int plan_query(uint32_t nx, uint32_t N, int has_pinv, const gbdpcg_config *cfg, gbdpcg_plan_info *out)
 {
@@ -661,7 +739,14 @@ void gbdpcg_workspace_destroy(gbdpcg_workspace *ws)
                                     void *stream)                                                                                   \
     { return build_pinv_dev<T>(S, P, nx, N, batch, kind, stream); }                                                                 \
     int gbdpcg_build_pinv_host_##SUF(gbdpcg_workspace *ws, const T *S, T *P, uint32_t nx, uint32_t N, uint32_t batch, int kind)     \
-    { return build_pinv_host<T>(ws, S, P, nx, N, batch, kind); }
+    { return build_pinv_host<T>(ws, S, P, nx, N, batch, kind); }                                                                   \
+    int gbdpcg_pack_csr_dev_##SUF(gbdpcg_workspace *, const uint32_t *rp, const uint32_t *ci, const T *v, uint32_t rows,           \
+                                  uint32_t nx, uint32_t N, T *out, int32_t *d_status, void *stream)                                 \
+    { return pack_csr_dev<T>(rp, ci, v, rows, nx, N, out, d_status, (cudaStream_t)stream); }                                        \
+    int gbdpcg_solve_csr_host_##SUF(gbdpcg_workspace *ws, const uint32_t *s_rp, const uint32_t *s_ci, const T *s_v, uint32_t s_nnz, \
+                                    const uint32_t *p_rp, const uint32_t *p_ci, const T *p_v, uint32_t p_nnz, const T *g, T *l,     \
+                                    uint32_t nx, uint32_t N, const gbdpcg_config *cfg, uint32_t *iters, int32_t *mie)               \
+    { return solve_csr_host<T>(ws, HostCsr{s_rp, s_ci, s_v, s_nnz}, HostCsr{p_rp, p_ci, p_v, p_nnz}, g, l, nx, N, cfg, iters, mie); }
 
 DEFINE_TYPED(f32, float)
 DEFINE_TYPED(f64, double)

@@ -158,6 +158,28 @@ GBDPCG_API int gbdpcg_build_pinv_host_f32(gbdpcg_workspace *ws, const float *h_S
 GBDPCG_API int gbdpcg_build_pinv_host_f64(gbdpcg_workspace *ws, const double *h_S, double *h_Pinv, uint32_t nx, uint32_t N, uint32_t batch,
                                           int kind);
 
+/* -- CSR front end: replaces the reference's unimplemented overload
+ *    solvePCG(csr_t<T>* h_S, csr_t<T>* h_Pinv, T* h_gamma, T* h_lambda, stateSize, knotPoints, config)
+ *    (include/interface.cuh:8-20 prints "NOT IMPLEMENTED" and exits 12; csr_t<T>: include/types.cuh:7-15).
+ *    _pack_csr_dev: device CSR (rows = nx*N, uint32 row_ptr[rows+1] / col_ind[nnz], T val[nnz]) -> compressed
+ *      block-tridiagonal layout in d_out (zeroed by the call); duplicates are summed; an entry outside the band sets
+ *      bit 0 of *d_status (device int32, may be NULL) and is dropped.  Asynchronous on `stream`.
+ *    _solve_csr_host: blocking solve with S (and optionally Phi^-1) given as host CSR.  Phi^-1 is used when its arrays
+ *      are non-NULL and cfg->empty_pinv == 0; GBDPCG_FLAG_BUILD_* forms it from S instead.  Returns
+ *      GBDPCG_ERR_INVALID when an entry lies outside the block-tridiagonal band. */
+GBDPCG_API int gbdpcg_pack_csr_dev_f32(gbdpcg_workspace *ws, const uint32_t *d_row_ptr, const uint32_t *d_col_ind, const float *d_val,
+                                       uint32_t rows, uint32_t nx, uint32_t N, float *d_out, int32_t *d_status, void *stream);
+GBDPCG_API int gbdpcg_pack_csr_dev_f64(gbdpcg_workspace *ws, const uint32_t *d_row_ptr, const uint32_t *d_col_ind, const double *d_val,
+                                       uint32_t rows, uint32_t nx, uint32_t N, double *d_out, int32_t *d_status, void *stream);
+GBDPCG_API int gbdpcg_solve_csr_host_f32(gbdpcg_workspace *ws, const uint32_t *S_row_ptr, const uint32_t *S_col_ind, const float *S_val,
+                                         uint32_t S_nnz, const uint32_t *P_row_ptr, const uint32_t *P_col_ind, const float *P_val,
+                                         uint32_t P_nnz, const float *h_gamma, float *h_lambda, uint32_t nx, uint32_t N,
+                                         const gbdpcg_config *cfg, uint32_t *iters, int32_t *max_iter_exit);
+GBDPCG_API int gbdpcg_solve_csr_host_f64(gbdpcg_workspace *ws, const uint32_t *S_row_ptr, const uint32_t *S_col_ind, const double *S_val,
+                                         uint32_t S_nnz, const uint32_t *P_row_ptr, const uint32_t *P_col_ind, const double *P_val,
+                                         uint32_t P_nnz, const double *h_gamma, double *h_lambda, uint32_t nx, uint32_t N,
+                                         const gbdpcg_config *cfg, uint32_t *iters, int32_t *max_iter_exit);
+
 /* -- launch-plan query: replaces pcgSharedMemSize<T> (reference include/pcg.cuh:13-20) and
  *    checkPcgOccupancy<T> (include/pcg.cuh:23-49) with what THIS library would launch. */
 typedef struct gbdpcg_plan_info {

@@ -6,10 +6,11 @@
 // Differences from the reference, all deliberate:
 //   * run-time (stateSize, knotPoints) are honoured; -DSTATE_SIZE/-DKNOT_POINTS are not needed;
 //   * the host-pointer overload returns the iteration count (the reference returns 1, interface.cuh:88),
-//     uses the identity preconditioner when none is supplied (the reference reads uninitialised device
-//     memory, interface.cuh:45-46) and does not copy S / gamma back;
+//     uses the identity preconditioner when empty_pinv != 0 and, when empty_pinv == 0, a preconditioner it forms
+//     from S on the device (config->pinv_build; the reference prints a warning and reads uninitialised device
+//     memory, interface.cuh:33-34,45-46), and does not copy S / gamma back;
 //   * no allocation per call (cached workspace inside the library);
-//   * the CSR overload is still not implemented and keeps the reference's behaviour (message + exit(12)).
+//   * the CSR overload, a stub in the reference (message + exit(12)), is implemented: CSR -> compressed layout on the device.
 #pragma once
 #include <cstdint>
 #include <cstdio>
@@ -49,6 +50,10 @@ struct abi<float> {
     static int dev(const float *S, const float *P, const float *g, float *l, uint32_t nx, uint32_t N, const gbdpcg_config *c,
                    uint32_t *it, int32_t *ex, void *stream)
     { return gbdpcg_solve_dev_sync_f32(nullptr, S, P, g, l, nx, N, c, it, ex, stream); }
+    static int csr(const uint32_t *srp, const uint32_t *sci, const float *sv, uint32_t snnz, const uint32_t *prp, const uint32_t *pci,
+                   const float *pv, uint32_t pnnz, const float *g, float *l, uint32_t nx, uint32_t N, const gbdpcg_config *c, uint32_t *it,
+                   int32_t *ex)
+    { return gbdpcg_solve_csr_host_f32(nullptr, srp, sci, sv, snnz, prp, pci, pv, pnnz, g, l, nx, N, c, it, ex); }
 };
 template <>
 struct abi<double> {
@@ -58,18 +63,45 @@ struct abi<double> {
     static int dev(const double *S, const double *P, const double *g, double *l, uint32_t nx, uint32_t N, const gbdpcg_config *c,
                    uint32_t *it, int32_t *ex, void *stream)
     { return gbdpcg_solve_dev_sync_f64(nullptr, S, P, g, l, nx, N, c, it, ex, stream); }
+    static int csr(const uint32_t *srp, const uint32_t *sci, const double *sv, uint32_t snnz, const uint32_t *prp, const uint32_t *pci,
+                   const double *pv, uint32_t pnnz, const double *g, double *l, uint32_t nx, uint32_t N, const gbdpcg_config *c,
+                   uint32_t *it, int32_t *ex)
+    { return gbdpcg_solve_csr_host_f64(nullptr, srp, sci, sv, snnz, prp, pci, pv, pnnz, g, l, nx, N, c, it, ex); }
 };
 
 }  // namespace gbdpcg_shim
 
-// ---- overload 1: S and Phi^-1 in CSR form (reference include/interface.cuh:8-20: a stub) -------------
+// ---- overload 1: S and Phi^-1 in CSR form (reference include/interface.cuh:8-20: a stub that prints
+//      "NOT IMPLEMENTED" and exits 12).  Implemented here: the CSR arrays (host pointers inside csr_t<T>,
+//      include/types.cuh:7-15) are packed into the compressed block-tridiagonal layout on the device.
+//      h_Pinv may be NULL; it is applied when config->empty_pinv == 0.  With h_Pinv == NULL and
+//      config->empty_pinv == 0 the library forms config->pinv_build from S on the device.
 template <typename T>
-uint32_t solvePCG(csr_t<T> * /*h_S*/, csr_t<T> * /*h_Pinv*/, T * /*h_gamma*/, T * /*h_lambda*/, unsigned /*stateSize*/,
-                  unsigned /*knotPoints*/, pcg_config<T> * /*config*/)
+uint32_t solvePCG(csr_t<T> *h_S, csr_t<T> *h_Pinv, T *h_gamma, T *h_lambda, unsigned stateSize, unsigned knotPoints,
+                  pcg_config<T> *config)
 {
-    std::cout << "NOT IMPLEMENTED" << std::endl;
-    std::exit(12);
-    return 0;
+    pcg_config<T> defaults;
+    if (!config) config = &defaults;
+    if (!h_S) { std::fprintf(stderr, "[Error] h_S must not be NULL\n"); std::exit(1); }
+    gbdpcg_config c = config->to_c();
+    if (!h_Pinv) {
+        if (!config->empty_pinv && config->pinv_build != GBDPCG_PINV_IDENTITY)
+            c.flags |= (config->pinv_build == GBDPCG_PINV_JACOBI) ? GBDPCG_FLAG_BUILD_JACOBI : GBDPCG_FLAG_BUILD_STAIR;
+        else
+            c.empty_pinv = 1;
+    }
+    if (h_S->rows != stateSize * knotPoints || h_S->cols != h_S->rows) {
+        std::fprintf(stderr, "[Error] CSR S must be square with stateSize*knotPoints rows\n");
+        std::exit(1);
+    }
+    uint32_t iters = 0;
+    int32_t hit_max = 0;
+    gbdpcg_shim::die_on_error(gbdpcg_shim::abi<T>::csr(h_S->row_ptr, h_S->col_ind, h_S->val, h_S->nnz, h_Pinv ? h_Pinv->row_ptr : nullptr,
+                                                       h_Pinv ? h_Pinv->col_ind : nullptr, h_Pinv ? h_Pinv->val : nullptr,
+                                                       h_Pinv ? h_Pinv->nnz : 0u, h_gamma, h_lambda, stateSize, knotPoints, &c, &iters,
+                                                       &hit_max),
+                              __FILE__, __LINE__);
+    return iters;
 }
 
 // ---- overload 2: host pointers, S in the compressed block-tridiagonal layout -----------------------
@@ -79,9 +111,12 @@ uint32_t solvePCG(T *h_S, T *h_gamma, T *h_lambda, unsigned stateSize, unsigned 
 {
     pcg_config<T> defaults;
     if (!config) config = &defaults;
-    if (!config->empty_pinv) std::cout << "This api can only be called with no preconditioner" << std::endl;
     gbdpcg_config c = config->to_c();
-    c.empty_pinv = 1;  // no Phi^-1 argument on this overload: identity
+    if (!config->empty_pinv && config->pinv_build != GBDPCG_PINV_IDENTITY)
+        // no Phi^-1 argument on this overload: the library forms it from S on the device (gbdpcg_build_pinv_*)
+        c.flags |= (config->pinv_build == GBDPCG_PINV_JACOBI) ? GBDPCG_FLAG_BUILD_JACOBI : GBDPCG_FLAG_BUILD_STAIR;
+    else
+        c.empty_pinv = 1;  // identity
     uint32_t iters = 0;
     int32_t hit_max = 0;
     gbdpcg_shim::die_on_error(gbdpcg_shim::abi<T>::host(h_S, nullptr, h_gamma, h_lambda, stateSize, knotPoints, &c, &iters, &hit_max),

@@ -20,6 +20,10 @@ struct csr_t {
 // Solver options.  pcg_exit_tol: absolute bound on |r . Phi^-1 r| (strict <); pcg_max_iter: iteration
 // cap; pcg_grid / pcg_block: carried, not used (as in the reference); empty_pinv: non-zero = no
 // preconditioner supplied -> identity.
+// Extension (trailing, defaulted; the reference's five fields keep their names, order and defaults): pinv_build
+// selects what the host-pointer overload -- which has no Phi^-1 argument -- does when empty_pinv == 0: it forms
+// Phi^-1 from S on the device (GBDPCG_PINV_STAIR by default, or GBDPCG_PINV_JACOBI).  The reference prints a
+// warning there and solves with uninitialised memory (include/interface.cuh:33-34,45-46).
 template <typename T>
 struct pcg_config {
     T pcg_exit_tol;
@@ -27,6 +31,7 @@ struct pcg_config {
     dim3 pcg_grid;
     dim3 pcg_block;
     int empty_pinv;
+    int pinv_build = GBDPCG_PINV_STAIR;
 
     pcg_config(T exit_tol = pcg_constants::DEFAULT_EPSILON<T>, uint32_t max_iter = pcg_constants::DEFAULT_MAX_PCG_ITER,
                dim3 grid = pcg_constants::DEFAULT_GRID, dim3 block = pcg_constants::DEFAULT_BLOCK, int empty_pinv = 1)

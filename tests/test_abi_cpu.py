@@ -116,7 +116,7 @@ def test_invalid_arguments_are_rejected_before_any_cuda_call():
 
 
 @pytest.mark.skipif(shutil.which("nvcc") is None, reason="needs nvcc")
-@pytest.mark.parametrize("example", ["pcg_solve.cu", "pcg_solve_dp.cu"])
+@pytest.mark.parametrize("example", ["pcg_solve.cu", "pcg_solve_dp.cu", "pcg_solve_csr.cu"])
 def test_reference_style_example_compiles_against_the_new_headers(example, tmp_path):
     """Acceptance of the header shim: a program written against the reference's
     gpu_pcg.cuh / solvePCG<T> builds with -I include -lgbdpcg.  Uses the reference's own example where the

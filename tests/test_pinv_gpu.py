@@ -160,3 +160,47 @@ def test_batched_host_solve_with_device_built_preconditioner():
         assert rel_err(lam_b[i], x) < 2e-4
     for i in range(16, B):
         assert np.array_equal(lam_b[i], lam_b[i % 16])
+
+
+def test_reference_signature_builds_the_preconditioner_when_empty_pinv_is_zero():
+    """solvePCG(h_S, h_gamma, h_lambda, stateSize, knotPoints, &config) with config.empty_pinv = 0: the reference warns
+    and solves with uninitialised memory (include/interface.cuh:33-34,45-46); here Phi^-1 (config.pinv_build) is formed
+    on the device, and the iteration counts are those of SURVEY s8(d): 103 / 50 / 25 for identity / Jacobi / stair."""
+    S, _, gam, nx, N, tol, max_iter = make_system("C2", "identity")
+    for kw, want in ((dict(empty_pinv=1), 103), (dict(empty_pinv=0, pinv_build="jacobi"), 50), (dict(empty_pinv=0), 25)):
+        lam = np.zeros(N * nx, dtype=S.dtype)
+        it = g.solvePCG(S, gam, lam, nx, N, g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, **kw))
+        assert abs(it - want) <= 1, (kw, it)
+
+
+def test_build_and_solve_are_capturable_in_a_cuda_graph():
+    """resident MPC loop -- build Phi^-1 + solve captured once, replayed with new S / gamma."""
+    torch = _torch()
+    nx, nu, N = 14, 7, 32
+    cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0)
+    S0, _, g0 = g.synth.lqr_schur(nx, nu, N, 0, "identity", np.float32)
+    d_S, d_g = torch.from_numpy(S0).cuda(), torch.from_numpy(g0).cuda()
+    d_P, d_l = torch.empty_like(d_S), torch.zeros(N * nx, device="cuda")
+    d_it = torch.zeros(1, dtype=torch.int32, device="cuda")
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        for _ in range(2):                        # warm-up outside capture (function attributes, occupancy queries)
+            d_l.zero_()
+            g.build_pinv_dev(nx, N, 1, d_S, d_P, "stair", stream=side)
+            g.solve_dev_async(nx, N, d_S, d_P, d_g, d_l, cfg, d_it, None, stream=side)
+    side.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=side):
+        d_l.zero_()
+        g.build_pinv_dev(nx, N, 1, d_S, d_P, "stair", stream=side)
+        g.solve_dev_async(nx, N, d_S, d_P, d_g, d_l, cfg, d_it, None, stream=side)
+    for seed in (3, 4, 5):
+        S1, P1, g1 = g.synth.lqr_schur(nx, nu, N, seed, "stair", np.float32)
+        d_S.copy_(torch.from_numpy(S1).cuda())
+        d_g.copy_(torch.from_numpy(g1).cuda())
+        graph.replay()
+        torch.cuda.synchronize()
+        lam_o, it_o, _ = oracle.pcg(S1, P1, g1, np.zeros(N * nx, np.float32), nx, N, 1e-6, 1000)
+        assert abs(int(d_it.item()) - it_o) <= 1
+        A = g.layout.unpack_dense(S1.astype(np.float64), nx, N)
+        assert rel_err(d_l.cpu().numpy(), np.linalg.solve(A, g1.astype(np.float64))) < 2e-4
