@@ -105,6 +105,9 @@ def measured_traffic(batch):
 
 
 def dist_env():
+    # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) off it
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -475,7 +478,14 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH, help="systems per GPU")
     ap.add_argument("--ref-sample", type=int, default=512, help="systems per step of the reference arm")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: everything libraries print meanwhile (NCCL's version banner, ...) goes to stderr
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
+    os.close(real_stdout)
     if out is not None:
         print(json.dumps(out), flush=True)
 
