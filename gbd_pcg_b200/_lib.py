@@ -61,6 +61,8 @@ for _s in ("f32", "f64"):
     SIGNATURES[f"gbdpcg_solve_batched_host_{_s}"] = (C.c_int, [_VP] * 5 + [_U32, _U32, _U32, _CFG, _VP, _VP])
     SIGNATURES[f"gbdpcg_build_pinv_dev_{_s}"] = (C.c_int, [_VP] * 3 + [_U32, _U32, _U32, C.c_int, _VP])
     SIGNATURES[f"gbdpcg_build_pinv_host_{_s}"] = (C.c_int, [_VP] * 3 + [_U32, _U32, _U32, C.c_int])
+    SIGNATURES[f"gbdpcg_schur_form_dev_{_s}"] = (C.c_int, [_VP] * 8 + [_U32] * 4 + [_VP] * 5)
+    SIGNATURES[f"gbdpcg_schur_recover_dev_{_s}"] = (C.c_int, [_VP] * 8 + [_U32] * 4 + [_VP] * 3)
     SIGNATURES[f"gbdpcg_pack_csr_dev_{_s}"] = (C.c_int, [_VP] * 4 + [_U32, _U32, _U32, _VP, _VP, _VP])
     SIGNATURES[f"gbdpcg_solve_csr_host_{_s}"] = (C.c_int, [_VP] * 4 + [_U32] + [_VP] * 3 + [_U32, _VP, _VP, _U32, _U32, _CFG,
                                                             C.POINTER(_U32), C.POINTER(_I32)])

@@ -301,6 +301,29 @@ def build_pinv_host(h_S, state_size, knot_points, batch=1, kind="stair"):
     return out.reshape(h_S.shape) if h_S.size == ms else out
 
 
+def schur_form_dev(state_size, control_size, knot_points, batch, d_Q, d_R, d_A, d_B, d_q, d_r, d_c, d_S, d_gamma,
+                   d_Qinv=None, d_Rinv=None, stream=None):
+    """Enqueue the Schur-complement formation S = -C G^-1 C^T, gamma = C G^-1 g - c from stage-wise LQR data
+    (include/gbdpcg.h; SURVEY.md s8(f) rank 4: the step before the path, upstream of the reference)."""
+    suf = _torch_dtype_suffix(d_Q)
+    f = getattr(_lib.lib(), f"gbdpcg_schur_form_dev_{suf}")
+    _lib.check(f(None, *[_dev_ptr(t, n) for t, n in ((d_Q, "d_Q"), (d_R, "d_R"), (d_A, "d_A"), (d_B, "d_B"), (d_q, "d_q"),
+                                                     (d_r, "d_r"), (d_c, "d_c"))],
+                 int(state_size), int(control_size), int(knot_points), int(batch), _dev_ptr(d_S, "d_S"), _dev_ptr(d_gamma, "d_gamma"),
+                 _dev_ptr(d_Qinv, "d_Qinv", True), _dev_ptr(d_Rinv, "d_Rinv", True), _stream_ptr(stream)))
+
+
+def schur_recover_dev(state_size, control_size, knot_points, batch, d_Qinv, d_Rinv, d_A, d_B, d_q, d_r, d_lambda, d_x, d_u,
+                      stream=None):
+    """Enqueue the primal recovery x_k = -Q_k^-1 (q_k + lambda_k - A_k^T lambda_{k+1}), u_k = -R_k^-1 (r_k - B_k^T lambda_{k+1})."""
+    suf = _torch_dtype_suffix(d_Qinv)
+    f = getattr(_lib.lib(), f"gbdpcg_schur_recover_dev_{suf}")
+    _lib.check(f(None, *[_dev_ptr(t, n) for t, n in ((d_Qinv, "d_Qinv"), (d_Rinv, "d_Rinv"), (d_A, "d_A"), (d_B, "d_B"),
+                                                     (d_q, "d_q"), (d_r, "d_r"), (d_lambda, "d_lambda"))],
+                 int(state_size), int(control_size), int(knot_points), int(batch), _dev_ptr(d_x, "d_x"), _dev_ptr(d_u, "d_u"),
+                 _stream_ptr(stream)))
+
+
 def plan_query(state_size, knot_points, dtype=np.float32, has_pinv=True, config=None) -> dict:
     """What the library would launch for this shape (replaces pcgSharedMemSize / checkPcgOccupancy,
     reference include/pcg.cuh:13-49)."""

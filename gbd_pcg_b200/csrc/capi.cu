@@ -19,6 +19,7 @@
 #include "pcg_rows.cuh"
 #include "pinv_build.h"
 #include "csr_pack.cuh"
+#include "schur_form.cuh"
 
 namespace gbdpcg {
 
@@ -578,6 +579,46 @@ static int build_pinv_host(gbdpcg_workspace *user_ws, const T *hS, T *hP, uint32
     return GBDPCG_OK;
 }
 
+// ---- Schur-complement formation / primal recovery (the steps either side of the solve; schur_form.cuh) ----
+template <typename T>
+static int schur_form_dev(const T *Q, const T *R, const T *A, const T *B, const T *q, const T *r, const T *c, uint32_t nx, uint32_t nu,
+                          uint32_t N, uint32_t batch, T *S, T *gamma, T *Qinv, T *Rinv, cudaStream_t st)
+{
+    if (!Q || !R || !A || !B || !q || !r || !c || !S || !gamma) return fail(GBDPCG_ERR_INVALID, "stage data, S and gamma must not be NULL");
+    if (nx == 0 || nu == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0, nu > 0 and N >= 2");
+    if ((uint64_t)nx * N > (1u << 24)) return fail(GBDPCG_ERR_UNSUPPORTED, "system too large");
+    if (batch == 0) return GBDPCG_OK;
+    const size_t smem = schur_form_smem_elems(nx, nu) * sizeof(T) + 16;
+    if (smem > kMaxDynSmem) return fail(GBDPCG_ERR_UNSUPPORTED, "nx=%u nu=%u needs %zu B of shared memory (limit %zu)", nx, nu, smem, kMaxDynSmem);
+    const void *fn = (const void *)schur_form_kernel<T>;
+    int rc = prepare_fn(fn, false);
+    if (rc) return rc;
+    SchurArgs a;
+    a.Q = Q; a.R = R; a.A = A; a.B = B; a.q = q; a.r = r; a.c = c; a.S = S; a.gamma = gamma; a.Qinv = Qinv; a.Rinv = Rinv;
+    a.nx = nx; a.nu = nu; a.N = N; a.batch = batch;
+    const unsigned long long items = (unsigned long long)batch * N;
+    const uint32_t grid = (uint32_t)(items < 148ull * 16 ? items : 148ull * 16);
+    schur_form_kernel<T><<<grid, 128, smem, st>>>(a);
+    CK(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
+template <typename T>
+static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *B, const T *q, const T *r, const T *lambda, uint32_t nx,
+                             uint32_t nu, uint32_t N, uint32_t batch, T *x, T *u, cudaStream_t st)
+{
+    if (!Qinv || !Rinv || !A || !B || !q || !r || !lambda || !x || !u) return fail(GBDPCG_ERR_INVALID, "arguments must not be NULL");
+    if (nx == 0 || nu == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0, nu > 0 and N >= 2");
+    if (batch == 0) return GBDPCG_OK;
+    const unsigned long long items = (unsigned long long)batch * N;
+    const uint32_t grid = (uint32_t)(items < 148ull * 32 ? items : 148ull * 32);
+    schur_recover_kernel<T><<<grid, 64, (nx + nu) * sizeof(T) + 16, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
+    CK(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
 // ---- CSR front end (reference include/interface.cuh:8-20 is a stub) ----
 template <typename T>
 static int pack_csr_dev(const uint32_t *row_ptr, const uint32_t *col_ind, const T *val, uint32_t rows, uint32_t nx, uint32_t N,
@@ -740,6 +781,14 @@ void gbdpcg_workspace_destroy(gbdpcg_workspace *ws)
     { return build_pinv_dev<T>(S, P, nx, N, batch, kind, stream); }                                                                 \
     int gbdpcg_build_pinv_host_##SUF(gbdpcg_workspace *ws, const T *S, T *P, uint32_t nx, uint32_t N, uint32_t batch, int kind)     \
     { return build_pinv_host<T>(ws, S, P, nx, N, batch, kind); }                                                                   \
+    int gbdpcg_schur_form_dev_##SUF(gbdpcg_workspace *, const T *Q, const T *R, const T *A, const T *B, const T *q, const T *r,      \
+                                    const T *c, uint32_t nx, uint32_t nu, uint32_t N, uint32_t batch, T *S, T *gamma, T *Qinv,      \
+                                    T *Rinv, void *stream)                                                                          \
+    { return schur_form_dev<T>(Q, R, A, B, q, r, c, nx, nu, N, batch, S, gamma, Qinv, Rinv, (cudaStream_t)stream); }                \
+    int gbdpcg_schur_recover_dev_##SUF(gbdpcg_workspace *, const T *Qinv, const T *Rinv, const T *A, const T *B, const T *q,        \
+                                       const T *r, const T *lambda, uint32_t nx, uint32_t nu, uint32_t N, uint32_t batch, T *x,     \
+                                       T *u, void *stream)                                                                          \
+    { return schur_recover_dev<T>(Qinv, Rinv, A, B, q, r, lambda, nx, nu, N, batch, x, u, (cudaStream_t)stream); }                  \
     int gbdpcg_pack_csr_dev_##SUF(gbdpcg_workspace *, const uint32_t *rp, const uint32_t *ci, const T *v, uint32_t rows,           \
                                   uint32_t nx, uint32_t N, T *out, int32_t *d_status, void *stream)                                 \
     { return pack_csr_dev<T>(rp, ci, v, rows, nx, N, out, d_status, (cudaStream_t)stream); }                                        \

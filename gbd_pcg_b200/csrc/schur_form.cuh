@@ -1,0 +1,222 @@
+// schur_form.cuh -- the steps either side of the solve: Schur-complement formation of
+// S and gamma from stage-wise LQR data, and recovery of the primal step from lambda.
+//
+// Not in the reference tree: upstream (MPCGPU, cited at reference README.md:66-76) forms S, gamma on the GPU before it
+// launches pcg<> (include/interface.cuh:92-103 is that seam); the reference's example input decodes to exactly this
+// construction and gbd_pcg_b200/synth.py is its host restatement.  Sign convention of the example
+// (S negative definite):  KKT  [G C^T; C 0][z; lambda] = [-g; -c],  G = blkdiag(Q_0, R_0, Q_1, R_1, ..., Q_{N-1}),
+// C row-block 0 = [I],  row-block k+1 = [-A_k  -B_k  I]   =>   S = -C G^-1 C^T,  gamma = C G^-1 g - c:
+//     S_00        = -Q_0^-1
+//     S_{k+1,k+1} = -(A_k Q_k^-1 A_k^T + B_k R_k^-1 B_k^T + Q_{k+1}^-1)
+//     S_{k+1,k}   =  A_k Q_k^-1            S_{k,k+1} = (A_k Q_k^-1)^T
+//     gamma_0     =  Q_0^-1 q_0 - c_0
+//     gamma_{k+1} = -A_k Q_k^-1 q_k - B_k R_k^-1 r_k + Q_{k+1}^-1 q_{k+1} - c_{k+1}
+// and after the solve   x_k = -Q_k^-1 (q_k + lambda_k - A_k^T lambda_{k+1}),   u_k = -R_k^-1 (r_k - B_k^T lambda_{k+1}).
+//
+// Inputs are stage-major, every matrix column-major:  Q [batch][N][nx*nx], R [batch][N-1][nu*nu], A [batch][N-1][nx*nx],
+// B [batch][N-1][nx*nu], q, c [batch][N][nx], r [batch][N-1][nu].  Output S in the solver's compressed layout
+// (reference include/pcg.cuh:104-110), padding blocks zero.
+//
+// One CTA per (system, block-row), run-time nx and nu, everything in shared memory.  Inversions: cooperative in-place
+// Gauss-Jordan without pivoting in the arithmetic order of glass::invertMatrix (GLASS/src/L3/inv.cuh:27-33), as in
+// pinv_build.cuh.  Q_j^-1 and A_j Q_j^-1 are formed by the two CTAs that need them (block-rows j and j+1).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gbdpcg {
+
+struct SchurArgs {
+    const void *Q, *R, *A, *B, *q, *r, *c;
+    void *S, *gamma, *Qinv, *Rinv;      // Qinv / Rinv optional by-products (for schur_recover)
+    uint32_t nx, nu, N, batch;
+};
+
+// elements of shared memory the forming kernel needs
+__host__ __device__ inline size_t schur_form_smem_elems(uint32_t nx, uint32_t nu)
+{
+    const size_t m = nx > nu ? nx : nu;
+    return (size_t)5 * nx * nx + (size_t)nu * nu + (size_t)2 * nx * nu + 2 * m + 3 * nx + nu;
+}
+
+// in-place inverse of the n x n column-major matrix Am (shared memory); colv / rowv: n elements of scratch each
+template <typename T>
+__device__ __forceinline__ void gj_invert_smem(T *Am, int n, T *colv, T *rowv)
+{
+    const int t = threadIdx.x, nthr = blockDim.x;
+    for (int p = 0; p < n; p++) {
+        for (int e = t; e < n; e += nthr) { colv[e] = Am[p * n + e]; rowv[e] = Am[e * n + p]; }
+        __syncthreads();
+        const T pv_inv = (T)1 / colv[p];
+        for (int e = t; e < n * n; e += nthr) {
+            const int c = e / n, r = e - c * n;
+            const T m = colv[r] * pv_inv;
+            T v;
+            if (r == p) v = (c == p) ? pv_inv : rowv[c] * pv_inv;
+            else v = (c == p) ? -m : Am[e] - m * rowv[c];
+            Am[e] = v;
+        }
+        __syncthreads();
+    }
+}
+
+// Cm (m x n) = Am (m x k) * Bm (k x n) [or Bm^T when TRANS_B: Bm is n x k], column-major, inner index ascending
+template <typename T, bool TRANS_B>
+__device__ __forceinline__ void mm_smem(const T *Am, const T *Bm, T *Cm, int m, int k, int n)
+{
+    for (int e = threadIdx.x; e < m * n; e += blockDim.x) {
+        const int c = e / m, r = e - c * m;
+        T s = (T)0;
+        for (int q = 0; q < k; q++) s += Am[q * m + r] * (TRANS_B ? Bm[q * n + c] : Bm[c * k + q]);
+        Cm[e] = s;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(128) schur_form_kernel(const SchurArgs a)
+{
+    extern __shared__ __align__(16) unsigned char schur_smem_raw[];
+    const int nx = (int)a.nx, nu = (int)a.nu, N = (int)a.N;
+    const int bb = nx * nx, uu = nu * nu, xu = nx * nu, mx = nx > nu ? nx : nu;
+    T *Qk = reinterpret_cast<T *>(schur_smem_raw);   // Q_k^-1   (k = j-1)
+    T *Qj = Qk + bb;                                  // Q_j^-1
+    T *AQ = Qj + bb;                                  // A_k Q_k^-1          = S_{j,j-1}
+    T *AQn = AQ + bb;                                 // A_j Q_j^-1          = S_{j+1,j}; its transpose is S_{j,j+1}
+    T *Dg = AQn + bb;                                 // diagonal block accumulator
+    T *Rk = Dg + bb;                                  // R_k^-1
+    T *BR = Rk + uu;                                  // B_k R_k^-1          (nx x nu)
+    T *Mt = BR + xu;                                  // staging for B_k     (A_k is staged in Dg)
+    T *colv = Mt + xu, *rowv = colv + mx;
+    T *v0 = rowv + mx, *v1 = v0 + nx, *v2 = v1 + nx, *vr = v2 + nx;   // q_k, q_j, c_j (nx each), r_k (nu)
+    const int t = threadIdx.x, nthr = blockDim.x;
+    const uint32_t items = a.batch * a.N;
+
+    for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
+        const uint32_t prob = item / a.N;
+        const int j = (int)(item - prob * a.N), k = j - 1;
+        const T *Q = static_cast<const T *>(a.Q) + ((size_t)prob * N) * bb;
+        const T *R = static_cast<const T *>(a.R) + ((size_t)prob * (N - 1)) * uu;
+        const T *A = static_cast<const T *>(a.A) + ((size_t)prob * (N - 1)) * bb;
+        const T *B = static_cast<const T *>(a.B) + ((size_t)prob * (N - 1)) * xu;
+        const T *q = static_cast<const T *>(a.q) + ((size_t)prob * N) * nx;
+        const T *r = static_cast<const T *>(a.r) + ((size_t)prob * (N - 1)) * nu;
+        const T *c = static_cast<const T *>(a.c) + ((size_t)prob * N) * nx;
+        T *Sr = static_cast<T *>(a.S) + ((size_t)prob * N + j) * 3 * bb;
+        T *gam = static_cast<T *>(a.gamma) + ((size_t)prob * N + j) * nx;
+
+        // ---- loads ----
+        for (int e = t; e < bb; e += nthr) { Qj[e] = Q[(size_t)j * bb + e]; if (k >= 0) Qk[e] = Q[(size_t)k * bb + e]; }
+        if (k >= 0) for (int e = t; e < uu; e += nthr) Rk[e] = R[(size_t)k * uu + e];
+        for (int e = t; e < nx; e += nthr) { v1[e] = q[(size_t)j * nx + e]; v2[e] = c[(size_t)j * nx + e]; if (k >= 0) v0[e] = q[(size_t)k * nx + e]; }
+        if (k >= 0) for (int e = t; e < nu; e += nthr) vr[e] = r[(size_t)k * nu + e];
+        __syncthreads();
+
+        // ---- inverses ----
+        gj_invert_smem<T>(Qj, nx, colv, rowv);
+        if (k >= 0) { gj_invert_smem<T>(Qk, nx, colv, rowv); gj_invert_smem<T>(Rk, nu, colv, rowv); }
+        if (a.Qinv) for (int e = t; e < bb; e += nthr) static_cast<T *>(a.Qinv)[((size_t)prob * N + j) * bb + e] = Qj[e];
+        if (a.Rinv && k >= 0) for (int e = t; e < uu; e += nthr) static_cast<T *>(a.Rinv)[((size_t)prob * (N - 1) + k) * uu + e] = Rk[e];
+
+        // ---- right block: S_{j,j+1} = (A_j Q_j^-1)^T ----
+        if (j + 1 < N) {
+            // AQn = A_j * Qj, reading A_j straight from global memory
+            const T *Aj = A + (size_t)j * bb;
+            for (int e = t; e < bb; e += nthr) {
+                const int cc = e / nx, rr = e - cc * nx;
+                T s = (T)0;
+                for (int p = 0; p < nx; p++) s += Aj[p * nx + rr] * Qj[cc * nx + p];
+                AQn[e] = s;
+            }
+            __syncthreads();
+            for (int e = t; e < bb; e += nthr) { const int cc = e / nx, rr = e - cc * nx; Sr[2 * bb + e] = AQn[rr * nx + cc]; }
+        } else {
+            for (int e = t; e < bb; e += nthr) Sr[2 * bb + e] = (T)0;
+        }
+
+        if (k < 0) {
+            // ---- block-row 0:  S_00 = -Q_0^-1, gamma_0 = Q_0^-1 q_0 - c_0 ----
+            for (int e = t; e < bb; e += nthr) { Sr[e] = (T)0; Sr[bb + e] = -Qj[e]; }
+            for (int e = t; e < nx; e += nthr) {
+                T s = (T)0;
+                for (int p = 0; p < nx; p++) s += Qj[p * nx + e] * v1[p];
+                gam[e] = s - v2[e];
+            }
+        } else {
+            // ---- block-row j = k+1 ----
+            const T *Ak = A + (size_t)k * bb, *Bk = B + (size_t)k * xu;
+            for (int e = t; e < bb; e += nthr) Dg[e] = Ak[e];                  // stage A_k
+            for (int e = t; e < xu; e += nthr) Mt[e] = Bk[e];                  // stage B_k
+            __syncthreads();
+            mm_smem<T, false>(Dg, Qk, AQ, nx, nx, nx);                         // AQ = A_k Q_k^-1
+            mm_smem<T, false>(Mt, Rk, BR, nx, nu, nu);                         // BR = B_k R_k^-1
+            __syncthreads();
+            for (int e = t; e < bb; e += nthr) Sr[e] = AQ[e];                  // left block
+            // diag = -((AQ A_k^T + BR B_k^T) + Q_j^-1);  A_k is still in Dg, B_k in Mt
+            for (int e = t; e < bb; e += nthr) {
+                const int cc = e / nx, rr = e - cc * nx;
+                T s = (T)0;
+                for (int p = 0; p < nx; p++) s += AQ[p * nx + rr] * Dg[p * nx + cc];
+                T s2 = (T)0;
+                for (int p = 0; p < nu; p++) s2 += BR[p * nx + rr] * Mt[p * nx + cc];
+                Sr[bb + e] = -((s + s2) + Qj[e]);
+            }
+            // gamma_j = ((Q_j^-1 q_j - AQ q_k) - BR r_k) - c_j
+            for (int e = t; e < nx; e += nthr) {
+                T s = (T)0, s1 = (T)0, s2 = (T)0;
+                for (int p = 0; p < nx; p++) { s += Qj[p * nx + e] * v1[p]; s1 += AQ[p * nx + e] * v0[p]; }
+                for (int p = 0; p < nu; p++) s2 += BR[p * nx + e] * vr[p];
+                gam[e] = ((s - s1) - s2) - v2[e];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// x_k = -Q_k^-1 (q_k + lambda_k - A_k^T lambda_{k+1}),  u_k = -R_k^-1 (r_k - B_k^T lambda_{k+1});  one CTA per (system, k)
+template <typename T>
+__global__ void __launch_bounds__(64) schur_recover_kernel(const T *__restrict__ Qinv, const T *__restrict__ Rinv, const T *__restrict__ A,
+                                                           const T *__restrict__ B, const T *__restrict__ q, const T *__restrict__ r,
+                                                           const T *__restrict__ lambda, T *__restrict__ x, T *__restrict__ u,
+                                                           uint32_t nx_, uint32_t nu_, uint32_t N_, uint32_t batch)
+{
+    extern __shared__ __align__(16) unsigned char schur_smem_raw[];
+    const int nx = (int)nx_, nu = (int)nu_, N = (int)N_;
+    T *tx = reinterpret_cast<T *>(schur_smem_raw), *tu = tx + nx;
+    const int t = threadIdx.x, nthr = blockDim.x;
+    const uint32_t items = batch * N_;
+    for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
+        const uint32_t prob = item / N_;
+        const int k = (int)(item - prob * N_);
+        const T *lam = lambda + (size_t)prob * N * nx;
+        const bool has_next = k + 1 < N;
+        const T *Ak = A + ((size_t)prob * (N - 1) + k) * nx * nx, *Bk = B + ((size_t)prob * (N - 1) + k) * nx * nu;
+        for (int e = t; e < nx; e += nthr) {
+            T s = (T)0;
+            if (has_next) for (int p = 0; p < nx; p++) s += Ak[e * nx + p] * lam[(size_t)(k + 1) * nx + p];      // (A_k^T lambda_{k+1})[e]
+            tx[e] = (q[((size_t)prob * N + k) * nx + e] + lam[(size_t)k * nx + e]) - s;
+        }
+        if (has_next) for (int e = t; e < nu; e += nthr) {
+            T s = (T)0;
+            for (int p = 0; p < nx; p++) s += Bk[e * nx + p] * lam[(size_t)(k + 1) * nx + p];                     // (B_k^T lambda_{k+1})[e]
+            tu[e] = r[((size_t)prob * (N - 1) + k) * nu + e] - s;
+        }
+        __syncthreads();
+        const T *Qi = Qinv + ((size_t)prob * N + k) * nx * nx;
+        for (int e = t; e < nx; e += nthr) {
+            T s = (T)0;
+            for (int p = 0; p < nx; p++) s += Qi[p * nx + e] * tx[p];
+            x[((size_t)prob * N + k) * nx + e] = -s;
+        }
+        if (has_next) {
+            const T *Ri = Rinv + ((size_t)prob * (N - 1) + k) * nu * nu;
+            for (int e = t; e < nu; e += nthr) {
+                T s = (T)0;
+                for (int p = 0; p < nu; p++) s += Ri[p * nu + e] * tu[p];
+                u[((size_t)prob * (N - 1) + k) * nu + e] = -s;
+            }
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace gbdpcg

@@ -72,6 +72,73 @@ def lqr_blocks(nx: int, nu: int, N: int, seed: int, *, a=0.8, dt=0.05, qpos=2.0,
     return diag, lower, gamma
 
 
+def lqr_stage_data(nx: int, nu: int, N: int, seed: int, dtype=np.float64, dense_costs: bool = False, **kw):
+    """Stage-wise LQR data of the same family as ``lqr_blocks`` in the layout of gbdpcg_schur_form_dev_*
+    (include/gbdpcg.h): Q [N, nx*nx], R [N-1, nu*nu], A [N-1, nx*nx], B [N-1, nx*nu] (each block column-major, flattened),
+    q, c [N, nx], r [N-1, nu].  With ``dense_costs=False`` the Schur complement of these data IS ``lqr_blocks``' S
+    (diagonal Q, R; terminal weight qN); ``dense_costs=True`` rotates Q_k, R_k into dense SPD matrices.
+    The linear terms q, r, c are extra draws from a second stream (seed + 2**31)."""
+    a, dt, qpos, qvel, rr, qN = (kw.get(k, d) for k, d in (("a", 0.8), ("dt", 0.05), ("qpos", 2.0), ("qvel", 0.5), ("r", 0.1), ("qN", 10.0)))
+    kscale, dscale = kw.get("kscale", 2.0), kw.get("dscale", 0.5)
+    nq = nx // 2
+    rng = np.random.default_rng(seed)
+    per_k = 2 * nq * nq + nq * nu
+    z = rng.standard_normal((N - 1) * per_k + N * nx)
+    zk = z[:(N - 1) * per_k].reshape(N - 1, per_k)
+    K = zk[:, :nq * nq].reshape(N - 1, nq, nq) * kscale
+    D = zk[:, nq * nq:2 * nq * nq].reshape(N - 1, nq, nq) * dscale
+    Bq = zk[:, 2 * nq * nq:].reshape(N - 1, nq, nu) * dt
+    A = np.zeros((N - 1, nx, nx))
+    A[:] = a * np.eye(nx)
+    A[:, :nq, nq:] += dt * np.eye(nq)
+    A[:, nq:, :nq] += dt * K
+    A[:, nq:, nq:] += dt * D
+    B = np.zeros((N - 1, nx, nu))
+    B[:, nq:, :] = Bq
+    qd = np.concatenate([np.full(nq, qpos), np.full(nx - nq, qvel)])
+    Q = np.stack([np.diag(qd)] * (N - 1) + [np.diag(qN * qd)])
+    R = np.stack([np.eye(nu) * rr] * (N - 1))
+    rng2 = np.random.default_rng(seed + 2 ** 31)
+    if dense_costs:
+        for k in range(N):
+            U, _ = np.linalg.qr(rng2.standard_normal((nx, nx)))
+            Q[k] = U @ Q[k] @ U.T
+            Q[k] = 0.5 * (Q[k] + Q[k].T)
+        for k in range(N - 1):
+            U, _ = np.linalg.qr(rng2.standard_normal((nu, nu)))
+            R[k] = U @ (R[k] * (1.0 + np.arange(nu))) @ U.T
+            R[k] = 0.5 * (R[k] + R[k].T)
+    q = rng2.standard_normal((N, nx))
+    r = rng2.standard_normal((N - 1, nu))
+    c = rng2.standard_normal((N, nx))
+    cm = lambda M: np.ascontiguousarray(np.swapaxes(M, 1, 2)).reshape(M.shape[0], -1).astype(dtype)     # column-major blocks
+    return {"Q": cm(Q), "R": cm(R), "A": cm(A), "B": cm(B), "q": q.astype(dtype), "r": r.astype(dtype), "c": c.astype(dtype)}
+
+
+def kkt_dense(data, nx: int, nu: int, N: int):
+    """Dense fp64 KKT matrix pieces (G, C, g, c) of the stage data, z ordered (x_0, u_0, x_1, ..., x_{N-1})."""
+    Q = data["Q"].astype(np.float64).reshape(N, nx, nx).swapaxes(1, 2)
+    R = data["R"].astype(np.float64).reshape(N - 1, nu, nu).swapaxes(1, 2)
+    A = data["A"].astype(np.float64).reshape(N - 1, nx, nx).swapaxes(1, 2)
+    B = data["B"].astype(np.float64).reshape(N - 1, nu, nx).swapaxes(1, 2)
+    nz = N * nx + (N - 1) * nu
+    G = np.zeros((nz, nz))
+    g = np.zeros(nz)
+    C = np.zeros((N * nx, nz))
+    xo = lambda k: k * (nx + nu)
+    uo = lambda k: k * (nx + nu) + nx
+    for k in range(N):
+        G[xo(k):xo(k) + nx, xo(k):xo(k) + nx] = Q[k]
+        g[xo(k):xo(k) + nx] = data["q"][k]
+        C[k * nx:(k + 1) * nx, xo(k):xo(k) + nx] = np.eye(nx)
+        if k + 1 < N:
+            G[uo(k):uo(k) + nu, uo(k):uo(k) + nu] = R[k]
+            g[uo(k):uo(k) + nu] = data["r"][k]
+            C[(k + 1) * nx:(k + 2) * nx, xo(k):xo(k) + nx] = -A[k]
+            C[(k + 1) * nx:(k + 2) * nx, uo(k):uo(k) + nu] = -B[k]
+    return G, C, g, data["c"].astype(np.float64).reshape(-1)
+
+
 def preconditioner_blocks(diag: np.ndarray, lower: np.ndarray, kind: str):
     """Phi^-1 blocks (diag, lower) in fp64 for kind in {'identity','jacobi','stair'}."""
     N, nx, _ = diag.shape

@@ -158,6 +158,31 @@ GBDPCG_API int gbdpcg_build_pinv_host_f32(gbdpcg_workspace *ws, const float *h_S
 GBDPCG_API int gbdpcg_build_pinv_host_f64(gbdpcg_workspace *ws, const double *h_S, double *h_Pinv, uint32_t nx, uint32_t N, uint32_t batch,
                                           int kind);
 
+/* -- the steps either side of the solve (not in the reference tree: upstream MPCGPU, cited at
+ *    reference README.md:66-76, forms S and gamma on the GPU before launching pcg<>, include/interface.cuh:92-103).
+ *    KKT system [G C^T; C 0][z; lambda] = [-g; -c] of the LQR sub-problem, G = blkdiag(Q_0, R_0, ..., Q_{N-1}),
+ *    C row-block 0 = [I], row-block k+1 = [-A_k -B_k I]:   S = -C G^-1 C^T,  gamma = C G^-1 g - c  (the sign convention
+ *    of the reference example, S negative definite):
+ *      S_00 = -Q_0^-1,  S_{k+1,k+1} = -(A_k Q_k^-1 A_k^T + B_k R_k^-1 B_k^T + Q_{k+1}^-1),  S_{k+1,k} = A_k Q_k^-1 = S_{k,k+1}^T
+ *      gamma_0 = Q_0^-1 q_0 - c_0,  gamma_{k+1} = -A_k Q_k^-1 q_k - B_k R_k^-1 r_k + Q_{k+1}^-1 q_{k+1} - c_{k+1}
+ *    _schur_form_dev: stage-major device inputs, every matrix column-major: Q [batch][N][nx*nx], R [batch][N-1][nu*nu],
+ *      A [batch][N-1][nx*nx], B [batch][N-1][nx*nu], q, c [batch][N][nx], r [batch][N-1][nu]; writes S (compressed layout,
+ *      padding blocks zero) and gamma; d_Qinv [batch][N][nx*nx] / d_Rinv [batch][N-1][nu*nu] are optional by-products.
+ *    _schur_recover_dev: x_k = -Q_k^-1 (q_k + lambda_k - A_k^T lambda_{k+1}), u_k = -R_k^-1 (r_k - B_k^T lambda_{k+1});
+ *      x [batch][N][nx], u [batch][N-1][nu].   Both asynchronous on `stream`. */
+GBDPCG_API int gbdpcg_schur_form_dev_f32(gbdpcg_workspace *ws, const float *d_Q, const float *d_R, const float *d_A, const float *d_B,
+                                         const float *d_q, const float *d_r, const float *d_c, uint32_t nx, uint32_t nu, uint32_t N,
+                                         uint32_t batch, float *d_S, float *d_gamma, float *d_Qinv, float *d_Rinv, void *stream);
+GBDPCG_API int gbdpcg_schur_form_dev_f64(gbdpcg_workspace *ws, const double *d_Q, const double *d_R, const double *d_A, const double *d_B,
+                                         const double *d_q, const double *d_r, const double *d_c, uint32_t nx, uint32_t nu, uint32_t N,
+                                         uint32_t batch, double *d_S, double *d_gamma, double *d_Qinv, double *d_Rinv, void *stream);
+GBDPCG_API int gbdpcg_schur_recover_dev_f32(gbdpcg_workspace *ws, const float *d_Qinv, const float *d_Rinv, const float *d_A,
+                                            const float *d_B, const float *d_q, const float *d_r, const float *d_lambda, uint32_t nx,
+                                            uint32_t nu, uint32_t N, uint32_t batch, float *d_x, float *d_u, void *stream);
+GBDPCG_API int gbdpcg_schur_recover_dev_f64(gbdpcg_workspace *ws, const double *d_Qinv, const double *d_Rinv, const double *d_A,
+                                            const double *d_B, const double *d_q, const double *d_r, const double *d_lambda, uint32_t nx,
+                                            uint32_t nu, uint32_t N, uint32_t batch, double *d_x, double *d_u, void *stream);
+
 /* -- CSR front end: replaces the reference's unimplemented overload
  *    solvePCG(csr_t<T>* h_S, csr_t<T>* h_Pinv, T* h_gamma, T* h_lambda, stateSize, knotPoints, config)
  *    (include/interface.cuh:8-20 prints "NOT IMPLEMENTED" and exits 12; csr_t<T>: include/types.cuh:7-15).

@@ -40,6 +40,12 @@ def lib():
             h = getattr(_lib, f"oracle_bdmv_{suf}")
             h.restype = None
             h.argtypes = [C.c_void_p] * 3 + [C.c_uint32, C.c_uint32]
+            sf = getattr(_lib, f"oracle_schur_form_{suf}")
+            sf.restype = C.c_int
+            sf.argtypes = [C.c_void_p] * 7 + [C.c_uint32] * 3 + [C.c_void_p] * 4
+            sr = getattr(_lib, f"oracle_schur_recover_{suf}")
+            sr.restype = C.c_int
+            sr.argtypes = [C.c_void_p] * 7 + [C.c_uint32] * 3 + [C.c_void_p] * 2
             b = getattr(_lib, f"oracle_build_pinv_{suf}")
             b.restype = C.c_int
             b.argtypes = [C.c_void_p] * 2 + [C.c_uint32, C.c_uint32, C.c_int]
@@ -112,6 +118,31 @@ def build_pinv(S, nx, N, kind):
         if rc != 0:
             raise ValueError("oracle_build_pinv: bad arguments")
     return P
+
+
+def schur_form(Q, R, A, B, q, r, c, nx, nu, N):
+    """One system: stage data (column-major matrices, see include/gbdpcg.h) -> (S, gamma, Qinv, Rinv)."""
+    dt = np.asarray(Q).dtype
+    arrs = [np.ascontiguousarray(a, dtype=dt) for a in (Q, R, A, B, q, r, c)]
+    S = np.empty(3 * N * nx * nx, dt)
+    gamma = np.empty(N * nx, dt)
+    Qinv = np.empty(N * nx * nx, dt)
+    Rinv = np.empty((N - 1) * nu * nu, dt)
+    rc = getattr(lib(), f"oracle_schur_form_{_suf(dt)}")(*[_ptr(a) for a in arrs], nx, nu, N, _ptr(S), _ptr(gamma), _ptr(Qinv), _ptr(Rinv))
+    if rc != 0:
+        raise ValueError("oracle_schur_form: bad arguments")
+    return S, gamma, Qinv, Rinv
+
+
+def schur_recover(Qinv, Rinv, A, B, q, r, lam, nx, nu, N):
+    dt = np.asarray(Qinv).dtype
+    arrs = [np.ascontiguousarray(a, dtype=dt) for a in (Qinv, Rinv, A, B, q, r, lam)]
+    x = np.empty(N * nx, dt)
+    u = np.empty((N - 1) * nu, dt)
+    rc = getattr(lib(), f"oracle_schur_recover_{_suf(dt)}")(*[_ptr(a) for a in arrs], nx, nu, N, _ptr(x), _ptr(u))
+    if rc != 0:
+        raise ValueError("oracle_schur_recover: bad arguments")
+    return x, u
 
 
 def pcg_numpy(S, Pinv, gamma, lambda0, nx, N, exit_tol, max_iter):

@@ -261,6 +261,108 @@ int FN(oracle_build_pinv)(const T *S, T *P, uint32_t nx, uint32_t N, int kind)
     return 0;
 }
 
+/* ---------------------------------------------------------------------------------------------
+ * Schur-complement formation and primal recovery (the steps either side
+ * of the solve).  Not in the reference tree (upstream MPCGPU, reference README.md:66-76); the
+ * construction is the one the reference example decodes to and that
+ * gbd_pcg_b200/synth.py restates on the host.  Formulae and layouts: include/gbdpcg.h.
+ * Same arithmetic order as the CUDA kernel (gbd_pcg_b200/csrc/schur_form.cuh): Gauss-Jordan in
+ * glass::invertMatrix order, inner indices ascending, diag = -((AQ A^T + BR B^T) + Qj^-1),
+ * gamma_j = ((Qj^-1 q_j - AQ q_k) - BR r_k) - c_j.
+ * Parity unpinned by the reference; pinned against a dense KKT solve in tests/test_schur_cpu.py.
+ * --------------------------------------------------------------------------------------------- */
+int FN(oracle_schur_form)(const T *Q, const T *R, const T *A, const T *B, const T *q, const T *r, const T *c,
+                          uint32_t nx, uint32_t nu, uint32_t N, T *S, T *gamma, T *Qinv, T *Rinv)
+{
+    if (!Q || !R || !A || !B || !q || !r || !c || !S || !gamma || nx == 0 || nu == 0 || N < 2) return -1;
+    size_t bb = (size_t)nx * nx, uu = (size_t)nu * nu, xu = (size_t)nx * nu, m = nx > nu ? nx : nu;
+    T *Qi = (T *)malloc(sizeof(T) * bb * N), *Ri = (T *)malloc(sizeof(T) * uu * (N - 1));
+    T *aug = (T *)malloc(sizeof(T) * (2 * m * m + m)), *s_temp = (T *)malloc(sizeof(T) * (2 * m + 1));
+    T *AQ = (T *)malloc(sizeof(T) * bb * (N - 1)), *BR = (T *)malloc(sizeof(T) * xu);
+    if (!Qi || !Ri || !aug || !s_temp || !AQ || !BR) { free(Qi); free(Ri); free(aug); free(s_temp); free(AQ); free(BR); return -2; }
+    for (uint32_t k = 0; k < N; k++) FN(invert_block)(Q + k * bb, Qi + k * bb, nx, aug, s_temp);
+    for (uint32_t k = 0; k + 1 < N; k++) FN(invert_block)(R + k * uu, Ri + k * uu, nu, aug, s_temp);
+    for (uint32_t k = 0; k + 1 < N; k++) FN(block_mm)(A + k * bb, Qi + k * bb, AQ + k * bb, nx);      /* A_k Q_k^-1 */
+    memset(S, 0, sizeof(T) * 3 * bb * N);
+    for (uint32_t j = 0; j < N; j++) {
+        T *Sr = S + (size_t)j * 3 * bb;
+        const T *Qj = Qi + j * bb;
+        if (j + 1 < N)                                                                              /* right = (A_j Q_j^-1)^T */
+            for (uint32_t cc = 0; cc < nx; cc++)
+                for (uint32_t rr = 0; rr < nx; rr++) Sr[2 * bb + (size_t)cc * nx + rr] = AQ[j * bb + (size_t)rr * nx + cc];
+        if (j == 0) {
+            for (size_t e = 0; e < bb; e++) Sr[bb + e] = -Qj[e];
+            for (uint32_t e = 0; e < nx; e++) {
+                T s = (T)0;
+                for (uint32_t p = 0; p < nx; p++) s += Qj[(size_t)p * nx + e] * q[p];
+                gamma[e] = s - c[e];
+            }
+            continue;
+        }
+        uint32_t k = j - 1;
+        const T *AQk = AQ + k * bb, *Ak = A + k * bb, *Bk = B + k * xu, *Rk = Ri + k * uu;
+        for (uint32_t cc = 0; cc < nu; cc++)                                                        /* BR = B_k R_k^-1 */
+            for (uint32_t rr = 0; rr < nx; rr++) {
+                T s = (T)0;
+                for (uint32_t p = 0; p < nu; p++) s += Bk[(size_t)p * nx + rr] * Rk[(size_t)cc * nu + p];
+                BR[(size_t)cc * nx + rr] = s;
+            }
+        memcpy(Sr, AQk, sizeof(T) * bb);                                                            /* left */
+        for (uint32_t cc = 0; cc < nx; cc++)
+            for (uint32_t rr = 0; rr < nx; rr++) {
+                T s = (T)0, s2 = (T)0;
+                for (uint32_t p = 0; p < nx; p++) s += AQk[(size_t)p * nx + rr] * Ak[(size_t)p * nx + cc];
+                for (uint32_t p = 0; p < nu; p++) s2 += BR[(size_t)p * nx + rr] * Bk[(size_t)p * nx + cc];
+                Sr[bb + (size_t)cc * nx + rr] = -((s + s2) + Qj[(size_t)cc * nx + rr]);
+            }
+        for (uint32_t e = 0; e < nx; e++) {
+            T s = (T)0, s1 = (T)0, s2 = (T)0;
+            for (uint32_t p = 0; p < nx; p++) { s += Qj[(size_t)p * nx + e] * q[(size_t)j * nx + p]; s1 += AQk[(size_t)p * nx + e] * q[(size_t)k * nx + p]; }
+            for (uint32_t p = 0; p < nu; p++) s2 += BR[(size_t)p * nx + e] * r[(size_t)k * nu + p];
+            gamma[(size_t)j * nx + e] = ((s - s1) - s2) - c[(size_t)j * nx + e];
+        }
+    }
+    if (Qinv) memcpy(Qinv, Qi, sizeof(T) * bb * N);
+    if (Rinv) memcpy(Rinv, Ri, sizeof(T) * uu * (N - 1));
+    free(Qi); free(Ri); free(aug); free(s_temp); free(AQ); free(BR);
+    return 0;
+}
+
+int FN(oracle_schur_recover)(const T *Qinv, const T *Rinv, const T *A, const T *B, const T *q, const T *r, const T *lambda,
+                             uint32_t nx, uint32_t nu, uint32_t N, T *x, T *u)
+{
+    if (!Qinv || !Rinv || !A || !B || !q || !r || !lambda || !x || !u || nx == 0 || nu == 0 || N < 2) return -1;
+    size_t bb = (size_t)nx * nx, uu = (size_t)nu * nu, xu = (size_t)nx * nu;
+    T *tx = (T *)malloc(sizeof(T) * (nx + nu)), *tu = tx + nx;
+    if (!tx) return -2;
+    for (uint32_t k = 0; k < N; k++) {
+        int has_next = k + 1 < N;
+        for (uint32_t e = 0; e < nx; e++) {
+            T s = (T)0;
+            if (has_next) for (uint32_t p = 0; p < nx; p++) s += A[k * bb + (size_t)e * nx + p] * lambda[(size_t)(k + 1) * nx + p];
+            tx[e] = (q[(size_t)k * nx + e] + lambda[(size_t)k * nx + e]) - s;
+        }
+        for (uint32_t e = 0; e < nx; e++) {
+            T s = (T)0;
+            for (uint32_t p = 0; p < nx; p++) s += Qinv[k * bb + (size_t)p * nx + e] * tx[p];
+            x[(size_t)k * nx + e] = -s;
+        }
+        if (!has_next) continue;
+        for (uint32_t e = 0; e < nu; e++) {
+            T s = (T)0;
+            for (uint32_t p = 0; p < nx; p++) s += B[k * xu + (size_t)e * nx + p] * lambda[(size_t)(k + 1) * nx + p];
+            tu[e] = r[(size_t)k * nu + e] - s;
+        }
+        for (uint32_t e = 0; e < nu; e++) {
+            T s = (T)0;
+            for (uint32_t p = 0; p < nu; p++) s += Rinv[k * uu + (size_t)p * nu + e] * tu[p];
+            u[(size_t)k * nu + e] = -s;
+        }
+    }
+    free(tx);
+    return 0;
+}
+
 #undef FN
 #undef CAT
 #undef CAT_
