@@ -588,14 +588,55 @@ static int schur_form_dev(const T *Q, const T *R, const T *A, const T *B, const 
     if (nx == 0 || nu == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0, nu > 0 and N >= 2");
     if ((uint64_t)nx * N > (1u << 24)) return fail(GBDPCG_ERR_UNSUPPORTED, "system too large");
     if (batch == 0) return GBDPCG_OK;
+    SchurArgs a;
+    a.Q = Q; a.R = R; a.A = A; a.B = B; a.q = q; a.r = r; a.c = c; a.S = S; a.gamma = gamma; a.Qinv = Qinv; a.Rinv = Rinv;
+    a.nx = nx; a.nu = nu; a.N = N; a.batch = batch;
+    int sms = 148, dev = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    // compiled state sizes with nu <= nx: chunked, lane-per-columns kernel
+    const void *fn_nx = nullptr;
+    if (nu <= nx) {
+        switch (nx) {
+#define CASE(NX) case NX: fn_nx = (const void *)schur_form_nx_kernel<T, NX>; break;
+            GBDPCG_FOR_EACH_NX(CASE)
+#undef CASE
+            default: break;
+        }
+    }
+    if (fn_nx) {
+        const int threads = 256;
+        int chunk = 0;
+        for (size_t budget : {(size_t)112 * 1024, kMaxDynSmem}) {
+            int c = (int)N;
+            while (c > 1 && schur_nx_smem_bytes<T>((int)nx, c, threads) > budget) c = (c + 1) / 2;
+            if (schur_nx_smem_bytes<T>((int)nx, c, threads) <= budget) { chunk = c; break; }
+        }
+        if (chunk > 0) {
+            if (chunk > 4 && (unsigned long long)batch * ((N + chunk - 1) / chunk) < (unsigned long long)sms) {
+                unsigned long long want = ((unsigned long long)batch * N + 2ull * sms - 1) / (2ull * sms);
+                int c = (int)(want < 4 ? 4 : want);
+                if (c < chunk) chunk = c;
+            }
+            const uint32_t nchunks = (N + chunk - 1) / chunk;
+            const size_t smem = schur_nx_smem_bytes<T>((int)nx, chunk, threads);
+            int rc = prepare_fn(fn_nx, false);
+            if (rc) return rc;
+            const unsigned long long items = (unsigned long long)batch * nchunks;
+            const int per_sm = smem <= (size_t)112 * 1024 ? 2 : 1;
+            const uint32_t grid = (uint32_t)(items < (unsigned long long)(sms * per_sm) ? items : (unsigned long long)(sms * per_sm));
+            uint32_t chunk_u = (uint32_t)chunk, nchunks_u = nchunks;
+            void *args[] = {&a, &chunk_u, &nchunks_u};
+            CK(cudaLaunchKernel(fn_nx, dim3(grid), dim3(threads), args, smem, st));
+            g_launches.fetch_add(1, std::memory_order_relaxed);
+            return GBDPCG_OK;
+        }
+    }
     const size_t smem = schur_form_smem_elems(nx, nu) * sizeof(T) + 16;
     if (smem > kMaxDynSmem) return fail(GBDPCG_ERR_UNSUPPORTED, "nx=%u nu=%u needs %zu B of shared memory (limit %zu)", nx, nu, smem, kMaxDynSmem);
     const void *fn = (const void *)schur_form_kernel<T>;
     int rc = prepare_fn(fn, false);
     if (rc) return rc;
-    SchurArgs a;
-    a.Q = Q; a.R = R; a.A = A; a.B = B; a.q = q; a.r = r; a.c = c; a.S = S; a.gamma = gamma; a.Qinv = Qinv; a.Rinv = Rinv;
-    a.nx = nx; a.nu = nu; a.N = N; a.batch = batch;
     const unsigned long long items = (unsigned long long)batch * N;
     const uint32_t grid = (uint32_t)(items < 148ull * 16 ? items : 148ull * 16);
     schur_form_kernel<T><<<grid, 128, smem, st>>>(a);

@@ -111,6 +111,46 @@ __device__ __forceinline__ void block_mv_bcast(const T *__restrict__ M, const T 
     }
 }
 
+// In-place Gauss-Jordan inversion of one NX x NX block spread over the NX/CPL lanes of a group: lane `li` holds columns
+// li*CPL .. li*CPL+CPL-1 in `col`.  Per pivot p the owner of column p publishes the scaled pivot column
+// m[r] = col_p[r] * pvInv (m[p] = pvInv) through the group's 16-element shared line `scr`; every lane then applies
+// a[r] -= m[r] * a[p], a[p] *= pvInv to its columns.  The owner first turns its column p into e_p, so the same update leaves
+// the image of the augmented identity column there: exactly the values of Gauss-Jordan on [A | I] in the arithmetic order
+// of glass::invertMatrix (reference GLASS/src/L3/inv.cuh:27-33).  All lanes of the warp must call it (__syncwarp inside);
+// lanes with valid == false compute on dummies.
+template <typename T, int NX, int CPL>
+__device__ __forceinline__ void gj_invert_cols(T (&col)[CPL][NX], const bool valid, const int li, T *scr)
+{
+    constexpr int V = PVec<T>::V;
+#pragma unroll
+    for (int p = 0; p < NX; p++) {
+        if (valid && li == p / CPL) {
+            const T pv_inv = (T)1 / col[p % CPL][p];
+#pragma unroll
+            for (int r = 0; r < NX; r++) {
+                scr[r] = (r == p) ? pv_inv : col[p % CPL][r] * pv_inv;
+                col[p % CPL][r] = (r == p) ? (T)1 : (T)0;
+            }
+        }
+        __syncwarp();
+        T m[NX + 4];
+#pragma unroll
+        for (int r = 0; r < NX; r += V) {
+            T x[4];
+            unpack_vec<T, V>(*reinterpret_cast<const typename PVec<T>::type *>(scr + r), x);
+#pragma unroll
+            for (int u = 0; u < V; u++) m[r + u] = x[u];
+        }
+#pragma unroll
+        for (int c = 0; c < CPL; c++) {
+            const T prv = col[c][p];
+#pragma unroll
+            for (int r = 0; r < NX; r++) col[c][r] = (r == p) ? prv * m[p] : col[c][r] - m[r] * prv;
+        }
+        __syncwarp();
+    }
+}
+
 template <typename T>
 __device__ __forceinline__ void copy_coalesced(T *__restrict__ dst, const T *__restrict__ src, int count, bool src_global)
 {
@@ -224,34 +264,7 @@ __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
 #pragma unroll
                         for (int r = 0; r < NX; r++) col[c][r] = src[c * NX + r];
                 }
-#pragma unroll
-                for (int p = 0; p < NX; p++) {
-                    constexpr int V = PVec<T>::V;
-                    if (valid && li == p / CPL) {
-                        const T pv_inv = (T)1 / col[p % CPL][p];
-#pragma unroll
-                        for (int r = 0; r < NX; r++) {
-                            scr1[r] = (r == p) ? pv_inv : col[p % CPL][r] * pv_inv;
-                            col[p % CPL][r] = (r == p) ? (T)1 : (T)0;
-                        }
-                    }
-                    __syncwarp();
-                    T m[NX + 4];
-#pragma unroll
-                    for (int r = 0; r < NX; r += V) {
-                        T x[4];
-                        unpack_vec<T, V>(*reinterpret_cast<const typename PVec<T>::type *>(scr1 + r), x);
-#pragma unroll
-                        for (int u = 0; u < V; u++) m[r + u] = x[u];
-                    }
-#pragma unroll
-                    for (int c = 0; c < CPL; c++) {
-                        const T prv = col[c][p];
-#pragma unroll
-                        for (int r = 0; r < NX; r++) col[c][r] = (r == p) ? prv * m[p] : col[c][r] - m[r] * prv;
-                    }
-                    __syncwarp();
-                }
+                gj_invert_cols<T, NX, CPL>(col, valid, li, scr1);
                 if (valid) {
                     T *d = dinv + (size_t)i * BB + li * CPL * NX;
 #pragma unroll

@@ -17,12 +17,18 @@
 // B [batch][N-1][nx*nu], q, c [batch][N][nx], r [batch][N-1][nu].  Output S in the solver's compressed layout
 // (reference include/pcg.cuh:104-110), padding blocks zero.
 //
-// One CTA per (system, block-row), run-time nx and nu, everything in shared memory.  Inversions: cooperative in-place
-// Gauss-Jordan without pivoting in the arithmetic order of glass::invertMatrix (GLASS/src/L3/inv.cuh:27-33), as in
-// pinv_build.cuh.  Q_j^-1 and A_j Q_j^-1 are formed by the two CTAs that need them (block-rows j and j+1).
+// Two kernels, same arithmetic order (Gauss-Jordan without pivoting as glass::invertMatrix, GLASS/src/L3/inv.cuh:27-33;
+// inner indices ascending):
+//   schur_form_nx_kernel<T, NX>  compiled state sizes, nu <= nx: a CTA takes a chunk of block-rows of one system, stages
+//     its stage data in shared memory (R_k, B_k padded to nx x nx with identity / zeros, which changes no value) and works
+//     with the lane-per-columns mapping of pinv_build.cuh: all inversions, then A_k Q_k^-1 and B_k R_k^-1, then the
+//     diagonal blocks and gamma; the S image leaves with coalesced 16-byte stores.
+//   schur_form_kernel<T>         run-time nx, nu fallback: one CTA per (system, block-row).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+
+#include "pinv_build.cuh"   // gj_invert_cols, block_mv_bcast, copy_coalesced, pinv_cpl
 
 namespace gbdpcg {
 
@@ -166,6 +172,210 @@ __global__ void __launch_bounds__(128) schur_form_kernel(const SchurArgs a)
                 for (int p = 0; p < nx; p++) { s += Qj[p * nx + e] * v1[p]; s1 += AQ[p * nx + e] * v0[p]; }
                 for (int p = 0; p < nu; p++) s2 += BR[p * nx + e] * vr[p];
                 gam[e] = ((s - s1) - s2) - v2[e];
+            }
+        }
+        __syncthreads();
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// specialised kernel
+// ---------------------------------------------------------------------------------------------------------------------
+// shared memory (elements): Qs, Rs, As, Bs [chunk+1][NX*NX] | img [chunk][3 NX*NX] | scratch | q, r [chunk+1][NX] | c [chunk][NX]
+template <typename T>
+__host__ __device__ inline size_t schur_nx_smem_bytes(int nx, int chunk, int threads)
+{
+    const int groups = (threads / 32) * (32 / (nx / pinv_cpl(nx)));
+    const size_t w = (size_t)chunk + 1, bb = (size_t)nx * nx;
+    return (4 * w * bb + 3 * (size_t)chunk * bb + 2 * w * nx + (size_t)chunk * nx + (size_t)groups * 16) * sizeof(T) + 32;
+}
+
+template <typename T, int NX>
+__global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_kernel(const SchurArgs a, const uint32_t chunk_, const uint32_t nchunks)
+{
+    constexpr int BB = NX * NX, BSZ = 3 * BB;
+    constexpr int CPL = pinv_cpl(NX), LPB = NX / CPL, GPW = 32 / LPB;
+    extern __shared__ __align__(16) unsigned char schur_smem_raw[];
+    const int chunk = (int)chunk_, W = chunk + 1, N = (int)a.N, nu = (int)a.nu;
+    T *Qs = reinterpret_cast<T *>(schur_smem_raw);
+    T *Rs = Qs + (size_t)W * BB, *As = Rs + (size_t)W * BB, *Bs = As + (size_t)W * BB;
+    T *img = Bs + (size_t)W * BB;
+    const int t = threadIdx.x, nthr = blockDim.x, lane = t & 31, warp = t >> 5;
+    const int gl = lane / LPB, li = lane - gl * LPB;
+    const bool lane_on = gl < GPW;
+    const int group = warp * GPW + gl, ngroups = (nthr >> 5) * GPW;
+    T *scr_all = img + (size_t)chunk * BSZ;                     // 16-byte aligned: read with vector loads
+    T *vq = scr_all + (size_t)ngroups * 16, *vr = vq + (size_t)W * NX, *vc = vr + (size_t)W * NX;
+    T *scr = scr_all + (lane_on ? group : 0) * 16;
+    const int c0 = li * CPL;                                    // first column this lane owns
+    const uint32_t items = a.batch * nchunks;
+
+    for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
+        const uint32_t prob = item / nchunks;
+        const int k0 = (int)(item - prob * nchunks) * chunk;
+        const int cnt = min(chunk, N - k0);
+        const T *Q = static_cast<const T *>(a.Q) + ((size_t)prob * N) * BB;
+        const T *R = static_cast<const T *>(a.R) + ((size_t)prob * (N - 1)) * nu * nu;
+        const T *A = static_cast<const T *>(a.A) + ((size_t)prob * (N - 1)) * BB;
+        const T *B = static_cast<const T *>(a.B) + ((size_t)prob * (N - 1)) * NX * nu;
+        const T *q = static_cast<const T *>(a.q) + ((size_t)prob * N) * NX;
+        const T *r = static_cast<const T *>(a.r) + ((size_t)prob * (N - 1)) * nu;
+        const T *c = static_cast<const T *>(a.c) + ((size_t)prob * N) * NX;
+        // slot i <-> knot kk = k0 - 1 + i;  row lb <-> block-row j = k0 + lb uses slot lb (knot j-1) and slot lb+1 (knot j)
+        const int i_lo = (k0 == 0) ? 1 : 0;                    // first slot that exists
+        auto knot = [&](int i) { return k0 - 1 + i; };
+
+        // ---- phase 0: stage the chunk's data ----
+        copy_coalesced<T>(Qs + (size_t)i_lo * BB, Q + (size_t)knot(i_lo) * BB, (cnt + 1 - i_lo) * BB, true);
+        {
+            const int hi = min(cnt, N - 2 - knot(0));           // last slot whose A / B / R exists
+            if (hi >= i_lo) copy_coalesced<T>(As + (size_t)i_lo * BB, A + (size_t)knot(i_lo) * BB, (hi + 1 - i_lo) * BB, true);
+            for (int e = t; e < (hi + 1 - i_lo) * BB; e += nthr) {
+                const int i = i_lo + e / BB, w = e % BB, cc = w / NX, rr = w - cc * NX, kk = knot(i);
+                Rs[(size_t)i * BB + w] = (rr < nu && cc < nu) ? R[(size_t)kk * nu * nu + cc * nu + rr] : ((rr == cc) ? (T)1 : (T)0);
+                Bs[(size_t)i * BB + w] = (cc < nu) ? B[(size_t)kk * NX * nu + cc * NX + rr] : (T)0;
+            }
+            for (int e = t; e < (hi + 1 - i_lo) * NX; e += nthr) {
+                const int i = i_lo + e / NX, w = e % NX;
+                vr[i * NX + w] = (w < nu) ? r[(size_t)knot(i) * nu + w] : (T)0;
+            }
+        }
+        for (int e = t; e < (cnt + 1 - i_lo) * NX; e += nthr) vq[i_lo * NX + e] = q[(size_t)knot(i_lo) * NX + e];
+        for (int e = t; e < cnt * NX; e += nthr) vc[e] = c[(size_t)k0 * NX + e];
+        __syncthreads();
+
+        // ---- phase 1: Q_kk^-1 (slots i_lo..cnt) and padded R_kk^-1 (slots i_lo..cnt-1, kk <= N-2), in place ----
+        for (int base = 0; base < 2 * W; base += ngroups) {
+            const int ti = base + group;
+            const bool isR = ti >= W;
+            const int i = isR ? ti - W : ti;
+            const bool valid = lane_on && ti < 2 * W && i >= i_lo && (isR ? (i <= cnt - 1 && knot(i) <= N - 2) : (i <= cnt));
+            T *blk = (isR ? Rs : Qs) + (size_t)(valid ? i : i_lo) * BB + c0 * NX;
+            T col[CPL][NX];
+#pragma unroll
+            for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                for (int rr = 0; rr < NX; rr++) col[cc][rr] = valid ? blk[cc * NX + rr] : ((rr == c0 + cc) ? (T)1 : (T)0);
+            gj_invert_cols<T, NX, CPL>(col, valid, li, scr);
+            if (valid) {
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                    for (int rr = 0; rr < NX; rr++) blk[cc * NX + rr] = col[cc][rr];
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 2: AQ_kk = A_kk Q_kk^-1 (left block of row kk+1, transposed: right block of row kk);
+        //               BR_kk = B_kk R_kk^-1 (parked in the diagonal slot of row kk+1) ----
+        for (int base = 0; base < 2 * W; base += ngroups) {
+            const int ti = base + group;
+            const bool isB = ti >= W;
+            const int i = isB ? ti - W : ti;
+            const bool valid = lane_on && ti < 2 * W && i >= i_lo && knot(i) <= N - 2 && (isB ? i <= cnt - 1 : i <= cnt);
+            if (valid) {
+                T x[CPL][NX], w[CPL][NX];
+                const T *X = (isB ? Rs : Qs) + (size_t)i * BB + c0 * NX;
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                    for (int rr = 0; rr < NX; rr++) x[cc][rr] = X[cc * NX + rr];
+                block_mv_bcast<T, NX, CPL>((isB ? Bs : As) + (size_t)i * BB, x, w);
+                if (isB) {
+#pragma unroll
+                    for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                        for (int rr = 0; rr < NX; rr++) img[(size_t)i * BSZ + BB + (c0 + cc) * NX + rr] = w[cc][rr];
+                } else {
+                    if (i <= cnt - 1) {
+#pragma unroll
+                        for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                            for (int rr = 0; rr < NX; rr++) img[(size_t)i * BSZ + (c0 + cc) * NX + rr] = w[cc][rr];
+                    }
+                    if (i >= 1) {
+#pragma unroll
+                        for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                            for (int rr = 0; rr < NX; rr++) img[(size_t)(i - 1) * BSZ + 2 * BB + rr * NX + (c0 + cc)] = w[cc][rr];
+                    }
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 3: diagonal blocks and gamma, row by row ----
+        for (int base = 0; base < cnt; base += ngroups) {
+            const int lb = base + group;
+            const bool valid = lane_on && lb < cnt;
+            const int lbv = valid ? lb : 0, j = k0 + lbv;
+            const T *Qj = Qs + (size_t)(lbv + 1) * BB;
+            T *row = img + (size_t)lbv * BSZ;
+            T out[CPL][NX];
+#pragma unroll
+            for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                for (int rr = 0; rr < NX; rr++) out[cc][rr] = -Qj[(c0 + cc) * NX + rr];
+            T gam[CPL];
+#pragma unroll
+            for (int cc = 0; cc < CPL; cc++) {
+                T s = (T)0;
+#pragma unroll
+                for (int p = 0; p < NX; p++) s += Qj[p * NX + c0 + cc] * vq[(lbv + 1) * NX + p];
+                gam[cc] = s;
+            }
+            if (valid && j > 0) {
+                T v[CPL][NX], w2[CPL][NX];
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                    for (int p = 0; p < NX; p++) v[cc][p] = As[(size_t)lbv * BB + p * NX + c0 + cc];       // row c0+cc of A_k
+                block_mv_bcast<T, NX, CPL>(row, v, out);                                                  // AQ A_k^T
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                    for (int p = 0; p < NX; p++) v[cc][p] = Bs[(size_t)lbv * BB + p * NX + c0 + cc];       // row c0+cc of B_k (padded)
+                block_mv_bcast<T, NX, CPL>(row + BB, v, w2);                                              // BR B_k^T
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++)
+#pragma unroll
+                    for (int rr = 0; rr < NX; rr++) out[cc][rr] = -((out[cc][rr] + w2[cc][rr]) + Qj[(c0 + cc) * NX + rr]);
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++) {
+                    T s1 = (T)0, s2 = (T)0;
+#pragma unroll
+                    for (int p = 0; p < NX; p++) {
+                        s1 += row[p * NX + c0 + cc] * vq[lbv * NX + p];
+                        s2 += row[BB + p * NX + c0 + cc] * vr[lbv * NX + p];
+                    }
+                    gam[cc] = (gam[cc] - s1) - s2;
+                }
+            }
+            __syncwarp();          // BR (parked in the diagonal slot) has been read by the whole group
+            if (valid) {
+#pragma unroll
+                for (int cc = 0; cc < CPL; cc++) {
+#pragma unroll
+                    for (int rr = 0; rr < NX; rr++) {
+                        row[BB + (c0 + cc) * NX + rr] = out[cc][rr];
+                        if (j == 0) row[(c0 + cc) * NX + rr] = (T)0;
+                        if (j == N - 1) row[2 * BB + (c0 + cc) * NX + rr] = (T)0;
+                    }
+                    static_cast<T *>(a.gamma)[((size_t)prob * N + j) * NX + c0 + cc] = gam[cc] - vc[lbv * NX + c0 + cc];
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 4: results ----
+        copy_coalesced<T>(static_cast<T *>(a.S) + ((size_t)prob * N + k0) * BSZ, img, cnt * BSZ, false);
+        if (a.Qinv) copy_coalesced<T>(static_cast<T *>(a.Qinv) + ((size_t)prob * N + k0) * BB, Qs + BB, cnt * BB, false);
+        if (a.Rinv) {
+            T *Ro = static_cast<T *>(a.Rinv) + ((size_t)prob * (N - 1)) * nu * nu;
+            for (int e = t; e < cnt * nu * nu; e += nthr) {
+                const int i = e / (nu * nu), w = e - i * nu * nu, cc = w / nu, rr = w - cc * nu, kk = knot(i);
+                if (i >= i_lo && kk <= N - 2) Ro[(size_t)kk * nu * nu + w] = Rs[(size_t)i * BB + cc * NX + rr];
             }
         }
         __syncthreads();
