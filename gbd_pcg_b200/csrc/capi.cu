@@ -653,8 +653,14 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
     if (nx == 0 || nu == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0, nu > 0 and N >= 2");
     if (batch == 0) return GBDPCG_OK;
     const unsigned long long items = (unsigned long long)batch * N;
-    const uint32_t grid = (uint32_t)(items < 148ull * 32 ? items : 148ull * 32);
-    schur_recover_kernel<T><<<grid, 64, (nx + nu) * sizeof(T) + 16, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
+    if (nx <= 32 && nu <= 32) {
+        const unsigned long long ctas = (items + 7) / 8;                       // one warp per (system, knot)
+        const uint32_t grid = (uint32_t)(ctas < 148ull * 8 ? ctas : 148ull * 8);
+        schur_recover_warp_kernel<T><<<grid, 256, 0, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
+    } else {
+        const uint32_t grid = (uint32_t)(items < 148ull * 32 ? items : 148ull * 32);
+        schur_recover_kernel<T><<<grid, 64, (nx + nu) * sizeof(T) + 16, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
+    }
     CK(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return GBDPCG_OK;

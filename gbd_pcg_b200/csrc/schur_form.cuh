@@ -429,4 +429,54 @@ __global__ void __launch_bounds__(64) schur_recover_kernel(const T *__restrict__
     }
 }
 
+// Warp-per-(system, knot) recovery for nx, nu <= 32: lane e owns row e; the intermediate vectors are exchanged with
+// shuffles, no shared memory, no block barrier.  Same arithmetic order as schur_recover_kernel.
+template <typename T>
+__global__ void __launch_bounds__(256) schur_recover_warp_kernel(const T *__restrict__ Qinv, const T *__restrict__ Rinv,
+                                                                 const T *__restrict__ A, const T *__restrict__ B, const T *__restrict__ q,
+                                                                 const T *__restrict__ r, const T *__restrict__ lambda, T *__restrict__ x,
+                                                                 T *__restrict__ u, uint32_t nx_, uint32_t nu_, uint32_t N_, uint32_t batch)
+{
+    const int nx = (int)nx_, nu = (int)nu_, N = (int)N_;
+    const int lane = threadIdx.x & 31;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t items = batch * N_;
+    for (uint32_t item = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; item < items; item += warps) {
+        const uint32_t prob = item / N_;
+        const int k = (int)(item - prob * N_);
+        const bool has_next = k + 1 < N;
+        const T *lam = lambda + (size_t)prob * N * nx;
+        const T ln = (has_next && lane < nx) ? lam[(size_t)(k + 1) * nx + lane] : (T)0;      // lambda_{k+1}[lane]
+        T tx = (T)0, tu = (T)0;
+        if (has_next) {
+            const T *Ak = A + ((size_t)prob * (N - 1) + k) * nx * nx, *Bk = B + ((size_t)prob * (N - 1) + k) * nx * nu;
+            T s = (T)0, s2 = (T)0;
+            for (int p = 0; p < nx; p++) {
+                const T lp = __shfl_sync(0xffffffffu, ln, p);
+                if (lane < nx) s += Ak[lane * nx + p] * lp;                                   // (A_k^T lambda_{k+1})[lane]
+                if (lane < nu) s2 += Bk[lane * nx + p] * lp;                                  // (B_k^T lambda_{k+1})[lane]
+            }
+            tx = s; tu = s2;
+        }
+        if (lane < nx) tx = (q[((size_t)prob * N + k) * nx + lane] + lam[(size_t)k * nx + lane]) - tx;
+        if (has_next && lane < nu) tu = r[((size_t)prob * (N - 1) + k) * nu + lane] - tu;
+        const T *Qi = Qinv + ((size_t)prob * N + k) * nx * nx;
+        T sx = (T)0;
+        for (int p = 0; p < nx; p++) {
+            const T tp = __shfl_sync(0xffffffffu, tx, p);
+            if (lane < nx) sx += Qi[p * nx + lane] * tp;
+        }
+        if (lane < nx) x[((size_t)prob * N + k) * nx + lane] = -sx;
+        if (has_next) {
+            const T *Ri = Rinv + ((size_t)prob * (N - 1) + k) * nu * nu;
+            T su = (T)0;
+            for (int p = 0; p < nu; p++) {
+                const T tp = __shfl_sync(0xffffffffu, tu, p);
+                if (lane < nu) su += Ri[p * nu + lane] * tp;
+            }
+            if (lane < nu) u[((size_t)prob * (N - 1) + k) * nu + lane] = -su;
+        }
+    }
+}
+
 }  // namespace gbdpcg
