@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -326,6 +327,8 @@ struct gbdpcg_workspace {
     size_t dcap[8] = {};
     uint32_t *d_iters = nullptr;
     uint8_t *d_exits = nullptr;
+    uint32_t *p_iters = nullptr;   // pinned host mirrors of the per-problem flags: a D2H copy into the caller's (pageable)
+    uint8_t *p_exits = nullptr;    // arrays would block the host inside the chunk loop and serialise copies and solves
     size_t cap_batch = 0;
     // mapped pinned scalars for the blocking single-solve calls: the kernel writes them in place
     uint32_t *h_iters = nullptr;
@@ -368,10 +371,14 @@ static int ws_reserve_flags(gbdpcg_workspace *w, size_t batch)
     if (w->cap_batch >= batch) return GBDPCG_OK;
     if (w->d_iters) { CK(cudaFree(w->d_iters)); w->d_iters = nullptr; }
     if (w->d_exits) { CK(cudaFree(w->d_exits)); w->d_exits = nullptr; }
+    if (w->p_iters) { CK(cudaFreeHost(w->p_iters)); w->p_iters = nullptr; }
+    if (w->p_exits) { CK(cudaFreeHost(w->p_exits)); w->p_exits = nullptr; }
     w->cap_batch = 0;
     size_t cap = batch + batch / 4 + 64;
     CK(cudaMalloc(&w->d_iters, cap * sizeof(uint32_t)));
     CK(cudaMalloc(&w->d_exits, cap));
+    CK(cudaHostAlloc((void **)&w->p_iters, cap * sizeof(uint32_t), cudaHostAllocDefault));
+    CK(cudaHostAlloc((void **)&w->p_exits, cap, cudaHostAllocDefault));
     w->cap_batch = cap;
     return GBDPCG_OK;
 }
@@ -381,6 +388,8 @@ static void ws_release(gbdpcg_workspace *w)
     for (auto &b : w->dbuf) if (b) cudaFree(b);
     if (w->d_iters) cudaFree(w->d_iters);
     if (w->d_exits) cudaFree(w->d_exits);
+    if (w->p_iters) cudaFreeHost(w->p_iters);
+    if (w->p_exits) cudaFreeHost(w->p_exits);
     if (w->h_iters) cudaFreeHost(w->h_iters);
     for (auto &s : w->streams) if (s) cudaStreamDestroy(s);
 }
@@ -532,7 +541,9 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     if ((rc = max_resident_problems(p, &resident))) return rc;
     if (resident < 1) resident = 1;
     // chunk = a whole number of resident waves, about 1/8 of the batch, at least 2 waves
-    size_t chunk = ((size_t)batch / 8 + resident - 1) / resident * resident;
+    size_t parts = 8;
+    if (const char *e = getenv("GBDPCG_HOST_CHUNKS")) { const long v = atol(e); if (v >= 1 && v <= 1024) parts = (size_t)v; }   // tuning knob
+    size_t chunk = ((size_t)batch / parts + resident - 1) / resident * resident;
     if (chunk < 2 * (size_t)resident) chunk = 2 * (size_t)resident;
     if (chunk > batch) chunk = batch;
 
@@ -550,11 +561,13 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
                        w->d_iters + o, w->d_exits + o, st);
         if (rc) return rc;
         CK(cudaMemcpyAsync(hl + o * ve, dl + o * ve, sizeof(T) * ve * n, cudaMemcpyDeviceToHost, st));
-        if (h_iters) CK(cudaMemcpyAsync(h_iters + o, w->d_iters + o, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, st));
-        if (h_exits) CK(cudaMemcpyAsync(h_exits + o, w->d_exits + o, n, cudaMemcpyDeviceToHost, st));
+        if (h_iters) CK(cudaMemcpyAsync(w->p_iters + o, w->d_iters + o, sizeof(uint32_t) * n, cudaMemcpyDeviceToHost, st));
+        if (h_exits) CK(cudaMemcpyAsync(w->p_exits + o, w->d_exits + o, n, cudaMemcpyDeviceToHost, st));
     }
     CK(cudaStreamSynchronize(w->streams[0]));
     CK(cudaStreamSynchronize(w->streams[1]));
+    if (h_iters) memcpy(h_iters, w->p_iters, sizeof(uint32_t) * batch);
+    if (h_exits) memcpy(h_exits, w->p_exits, batch);
     return GBDPCG_OK;
 }
 
