@@ -246,12 +246,16 @@ __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
             // column m[r] = col_p[r] * pvInv (m[p] = pvInv); every lane then applies a[r] -= m[r] * a[p], a[p] *= pvInv
             // to its columns.  The owner first turns its column p into e_p, so the same update leaves the image of
             // the augmented identity column there: exactly the values of Gauss-Jordan on [A | I] (inv.cuh:27-33).
-            const int ninv = cnt + 2;
+            // task list = the knots whose inverse is needed and exists (halo slots 0 and cnt+1 only for the stair kind)
+            const int i_first = (a.kind == PINV_STAIR && k0 > 0) ? 0 : 1;
+            const int i_last = (a.kind == PINV_STAIR && k0 + cnt < N) ? cnt + 1 : cnt;
+            const int ninv = i_last - i_first + 1;
             for (int base = 0; base < ninv; base += ngroups1) {
-                const int i = base + group1;
+                const int i = i_first + base + group1;
                 const int k = k0 - 1 + i;
                 const bool inside = i >= 1 && i <= cnt;
-                const bool valid = lane_on1 && i < ninv && k >= 0 && k < N && (inside || a.kind == PINV_STAIR);
+                const bool valid = lane_on1 && i <= i_last;
+                if (!__any_sync(0xffffffffu, valid)) continue;          // warp-uniform: this warp has no block in this round
                 T col[CPL][NX];
 #pragma unroll
                 for (int c = 0; c < CPL; c++)

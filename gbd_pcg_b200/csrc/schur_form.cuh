@@ -246,11 +246,14 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
         __syncthreads();
 
         // ---- phase 1: Q_kk^-1 (slots i_lo..cnt) and padded R_kk^-1 (slots i_lo..cnt-1, kk <= N-2), in place ----
-        for (int base = 0; base < 2 * W; base += ngroups) {
+        const int hi_ab = min(cnt, N - 1 - k0);                 // last slot whose A exists (knot <= N-2)
+        const int nQ = cnt + 1 - i_lo, nR = max(0, min(cnt - 1, hi_ab) - i_lo + 1);
+        for (int base = 0; base < nQ + nR; base += ngroups) {
             const int ti = base + group;
-            const bool isR = ti >= W;
-            const int i = isR ? ti - W : ti;
-            const bool valid = lane_on && ti < 2 * W && i >= i_lo && (isR ? (i <= cnt - 1 && knot(i) <= N - 2) : (i <= cnt));
+            const bool isR = ti >= nQ;
+            const int i = i_lo + (isR ? ti - nQ : ti);
+            const bool valid = lane_on && ti < nQ + nR;
+            if (!__any_sync(0xffffffffu, valid)) continue;      // warp-uniform
             T *blk = (isR ? Rs : Qs) + (size_t)(valid ? i : i_lo) * BB + c0 * NX;
             T col[CPL][NX];
 #pragma unroll
@@ -269,11 +272,12 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
 
         // ---- phase 2: AQ_kk = A_kk Q_kk^-1 (left block of row kk+1, transposed: right block of row kk);
         //               BR_kk = B_kk R_kk^-1 (parked in the diagonal slot of row kk+1) ----
-        for (int base = 0; base < 2 * W; base += ngroups) {
+        const int nA = max(0, hi_ab - i_lo + 1), nB = nR;
+        for (int base = 0; base < nA + nB; base += ngroups) {
             const int ti = base + group;
-            const bool isB = ti >= W;
-            const int i = isB ? ti - W : ti;
-            const bool valid = lane_on && ti < 2 * W && i >= i_lo && knot(i) <= N - 2 && (isB ? i <= cnt - 1 : i <= cnt);
+            const bool isB = ti >= nA;
+            const int i = i_lo + (isB ? ti - nA : ti);
+            const bool valid = lane_on && ti < nA + nB;
             if (valid) {
                 T x[CPL][NX], w[CPL][NX];
                 const T *X = (isB ? Rs : Qs) + (size_t)i * BB + c0 * NX;
@@ -309,6 +313,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
         for (int base = 0; base < cnt; base += ngroups) {
             const int lb = base + group;
             const bool valid = lane_on && lb < cnt;
+            if (!__any_sync(0xffffffffu, valid)) continue;      // warp-uniform
             const int lbv = valid ? lb : 0, j = k0 + lbv;
             const T *Qj = Qs + (size_t)(lbv + 1) * BB;
             T *row = img + (size_t)lbv * BSZ;

@@ -204,3 +204,31 @@ def test_build_and_solve_are_capturable_in_a_cuda_graph():
         assert abs(int(d_it.item()) - it_o) <= 1
         A = g.layout.unpack_dense(S1.astype(np.float64), nx, N)
         assert rel_err(d_l.cpu().numpy(), np.linalg.solve(A, g1.astype(np.float64))) < 2e-4
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+def test_unaligned_device_pointers_fall_back_from_tma(dt):
+    """S / Pinv not 16-byte aligned: the TMA bulk copies are replaced by ordinary loads and stores, same bits."""
+    torch = _torch()
+    nx, nu, N, B = 14, 7, 32, 5
+    S, _, _ = g.synth.lqr_schur_batch(nx, nu, N, range(B), "identity", dt)
+    ref = gpu_build(S, nx, N, B, "stair")
+    n = S.size
+    buf_s = torch.zeros(n + 3, dtype=torch.float32 if dt == np.float32 else torch.float64, device="cuda")
+    buf_p = torch.full((n + 3,), float("nan"), dtype=buf_s.dtype, device="cuda")
+    off = 1                                                   # 4- or 8-byte aligned only
+    buf_s[off:off + n].copy_(torch.from_numpy(S.reshape(-1)))
+    d_S, d_P = buf_s[off:off + n], buf_p[off:off + n]
+    assert d_S.data_ptr() % 16 != 0
+    g.build_pinv_dev(nx, N, B, d_S, d_P, "stair")
+    torch.cuda.synchronize()
+    assert np.array_equal(d_P.cpu().numpy().reshape(ref.shape), ref)
+    assert torch.isnan(buf_p[:off]).all() and torch.isnan(buf_p[off + n:]).all()     # nothing written outside
+
+
+def test_zero_batch_is_a_no_op():
+    torch = _torch()
+    x = torch.zeros(3 * 4 * 4 * 2, device="cuda")
+    before = g.kernel_launches()
+    g.build_pinv_dev(4, 2, 0, x, x.clone(), "stair")
+    assert g.kernel_launches() == before
