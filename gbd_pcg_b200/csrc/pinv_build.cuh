@@ -168,8 +168,44 @@ __device__ __forceinline__ void copy_coalesced(T *__restrict__ dst, const T *__r
             for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < total) d4[q] = v[u]; }
         }
     } else {
-        for (int q = t; q < count; q += nthr) dst[q] = src[q];
+        constexpr int U = 4;                                   // loads first, then stores: U requests in flight per thread
+        for (int base = 0; base < count; base += U * nthr) {
+            T v[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < count) v[u] = src[q]; }
+#pragma unroll
+            for (int u = 0; u < U; u++) { const int q = base + u * nthr + t; if (q < count) dst[q] = v[u]; }
+        }
     }
+}
+
+// Asynchronous global -> shared copy of `count` elements with cp.async (LDGSTS): 16-byte pieces when both sides are
+// 16-byte aligned, element-sized pieces otherwise.  Nothing is waited for here: issue several, then async_copy_wait().
+template <typename T>
+__device__ __forceinline__ void async_copy(T *__restrict__ dst, const T *__restrict__ src, int count)
+{
+    const int t = threadIdx.x, nthr = blockDim.x;
+    if (count <= 0) return;
+    if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0 && (pv_smem_u32(dst) & 15u) == 0 && (count * (int)sizeof(T)) % 16 == 0) {
+        const int total = count * (int)sizeof(T) / 16;
+        const uint32_t d0 = pv_smem_u32(dst);
+        const char *s0 = reinterpret_cast<const char *>(src);
+        for (int q = t; q < total; q += nthr)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 16u * (uint32_t)q), "l"(s0 + 16 * (size_t)q) : "memory");
+    } else {
+        const uint32_t d0 = pv_smem_u32(dst);
+        for (int q = t; q < count; q += nthr) {
+            if constexpr (sizeof(T) == 4)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4u * (uint32_t)q), "l"(src + q) : "memory");
+            else
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0 + 8u * (uint32_t)q), "l"(src + q) : "memory");
+        }
+    }
+}
+__device__ __forceinline__ void async_copy_wait()
+{
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 // columns of a block one lane owns during the inversion (2 halves the per-pivot overhead per block; 1 for tiny blocks)

@@ -36,7 +36,15 @@ struct SchurArgs {
     const void *Q, *R, *A, *B, *q, *r, *c;
     void *S, *gamma, *Qinv, *Rinv;      // Qinv / Rinv optional by-products (for schur_recover)
     uint32_t nx, nu, N, batch;
+#ifdef SCHUR_TRACE
+    unsigned long long *trace;          // [8] accumulated clock64 per phase (thread 0 of every CTA), scripts/ubench/trace_schur.cu
+#endif
 };
+#ifdef SCHUR_TRACE
+#define SCHUR_MARK(slot) do { if (threadIdx.x == 0) { const long long now_ = clock64(); atomicAdd(a.trace + (slot), (unsigned long long)(now_ - tmark_)); tmark_ = now_; } } while (0)
+#else
+#define SCHUR_MARK(slot) do { } while (0)
+#endif
 
 // elements of shared memory the forming kernel needs
 __host__ __device__ inline size_t schur_form_smem_elems(uint32_t nx, uint32_t nu)
@@ -182,13 +190,13 @@ __global__ void __launch_bounds__(128) schur_form_kernel(const SchurArgs a)
 // ---------------------------------------------------------------------------------------------------------------------
 // specialised kernel
 // ---------------------------------------------------------------------------------------------------------------------
-// shared memory (elements): Qs, Rs, As, Bs [chunk+1][NX*NX] | img [chunk][3 NX*NX] | scratch | q, r [chunk+1][NX] | c [chunk][NX]
+// shared memory (elements): Qs, Rs, As, Bs [chunk+1][NX*NX] | img [chunk][3 NX*NX] | scratch | q, r [chunk+1][NX] | c [chunk][NX] | r compact [chunk+1][NX]
 template <typename T>
 __host__ __device__ inline size_t schur_nx_smem_bytes(int nx, int chunk, int threads)
 {
     const int groups = (threads / 32) * (32 / (nx / pinv_cpl(nx)));
     const size_t w = (size_t)chunk + 1, bb = (size_t)nx * nx;
-    return (4 * w * bb + 3 * (size_t)chunk * bb + 2 * w * nx + (size_t)chunk * nx + (size_t)groups * 16) * sizeof(T) + 32;
+    return (4 * w * bb + 3 * (size_t)chunk * bb + 3 * w * nx + (size_t)chunk * nx + (size_t)groups * 16) * sizeof(T) + 32;
 }
 
 template <typename T, int NX>
@@ -206,7 +214,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
     const bool lane_on = gl < GPW;
     const int group = warp * GPW + gl, ngroups = (nthr >> 5) * GPW;
     T *scr_all = img + (size_t)chunk * BSZ;                     // 16-byte aligned: read with vector loads
-    T *vq = scr_all + (size_t)ngroups * 16, *vr = vq + (size_t)W * NX, *vc = vr + (size_t)W * NX;
+    T *vq = scr_all + (size_t)ngroups * 16, *vr = vq + (size_t)W * NX, *vc = vr + (size_t)W * NX, *vrc = vc + (size_t)chunk * NX;
     T *scr = scr_all + (lane_on ? group : 0) * 16;
     const int c0 = li * CPL;                                    // first column this lane owns
     const uint32_t items = a.batch * nchunks;
@@ -226,24 +234,39 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
         const int i_lo = (k0 == 0) ? 1 : 0;                    // first slot that exists
         auto knot = [&](int i) { return k0 - 1 + i; };
 
+#ifdef SCHUR_TRACE
+        long long tmark_ = clock64();
+#endif
         // ---- phase 0: stage the chunk's data ----
-        copy_coalesced<T>(Qs + (size_t)i_lo * BB, Q + (size_t)knot(i_lo) * BB, (cnt + 1 - i_lo) * BB, true);
+        // (every piece is an asynchronous cp.async copy: all of them are in flight together, one wait)
+        async_copy<T>(Qs + (size_t)i_lo * BB, Q + (size_t)knot(i_lo) * BB, (cnt + 1 - i_lo) * BB);
         {
             const int hi = min(cnt, N - 2 - knot(0));           // last slot whose A / B / R exists
-            if (hi >= i_lo) copy_coalesced<T>(As + (size_t)i_lo * BB, A + (size_t)knot(i_lo) * BB, (hi + 1 - i_lo) * BB, true);
-            for (int e = t; e < (hi + 1 - i_lo) * BB; e += nthr) {
-                const int i = i_lo + e / BB, w = e % BB, cc = w / NX, rr = w - cc * NX, kk = knot(i);
-                Rs[(size_t)i * BB + w] = (rr < nu && cc < nu) ? R[(size_t)kk * nu * nu + cc * nu + rr] : ((rr == cc) ? (T)1 : (T)0);
-                Bs[(size_t)i * BB + w] = (cc < nu) ? B[(size_t)kk * NX * nu + cc * NX + rr] : (T)0;
+            const int ns = hi + 1 - i_lo;                       // slots with A / B / R
+            T *tmpR = img, *tmpB = img + (size_t)W * BB;        // compact copies parked in the (still unused) output image
+            if (ns > 0) {
+                async_copy<T>(As + (size_t)i_lo * BB, A + (size_t)knot(i_lo) * BB, ns * BB);
+                async_copy<T>(tmpR, R + (size_t)knot(i_lo) * nu * nu, ns * nu * nu);
+                async_copy<T>(tmpB, B + (size_t)knot(i_lo) * NX * nu, ns * NX * nu);
+                async_copy<T>(vrc, r + (size_t)knot(i_lo) * nu, ns * nu);
             }
-            for (int e = t; e < (hi + 1 - i_lo) * NX; e += nthr) {
-                const int i = i_lo + e / NX, w = e % NX;
-                vr[i * NX + w] = (w < nu) ? r[(size_t)knot(i) * nu + w] : (T)0;
+            async_copy<T>(vq + i_lo * NX, q + (size_t)knot(i_lo) * NX, (cnt + 1 - i_lo) * NX);
+            async_copy<T>(vc, c + (size_t)k0 * NX, cnt * NX);
+            async_copy_wait();
+            __syncthreads();
+            for (int e = t; e < ns * NX; e += nthr) {
+                const int s_ = e / NX, w = e - s_ * NX;
+                vr[(i_lo + s_) * NX + w] = (w < nu) ? vrc[s_ * nu + w] : (T)0;
+            }
+            // expand R_k, B_k to nx x nx (identity / zero padding), shared -> shared
+            for (int e = t; e < ns * BB; e += nthr) {
+                const int s_ = e / BB, w = e - s_ * BB, cc = w / NX, rr = w - cc * NX;
+                Rs[(size_t)(i_lo + s_) * BB + w] = (rr < nu && cc < nu) ? tmpR[s_ * nu * nu + cc * nu + rr] : ((rr == cc) ? (T)1 : (T)0);
+                Bs[(size_t)(i_lo + s_) * BB + w] = (cc < nu) ? tmpB[s_ * NX * nu + cc * NX + rr] : (T)0;
             }
         }
-        for (int e = t; e < (cnt + 1 - i_lo) * NX; e += nthr) vq[i_lo * NX + e] = q[(size_t)knot(i_lo) * NX + e];
-        for (int e = t; e < cnt * NX; e += nthr) vc[e] = c[(size_t)k0 * NX + e];
         __syncthreads();
+        SCHUR_MARK(0);
 
         // ---- phase 1: Q_kk^-1 (slots i_lo..cnt) and padded R_kk^-1 (slots i_lo..cnt-1, kk <= N-2), in place ----
         const int hi_ab = min(cnt, N - 1 - k0);                 // last slot whose A exists (knot <= N-2)
@@ -269,6 +292,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
             }
         }
         __syncthreads();
+        SCHUR_MARK(1);
 
         // ---- phase 2: AQ_kk = A_kk Q_kk^-1 (left block of row kk+1, transposed: right block of row kk);
         //               BR_kk = B_kk R_kk^-1 (parked in the diagonal slot of row kk+1) ----
@@ -308,6 +332,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
             }
         }
         __syncthreads();
+        SCHUR_MARK(2);
 
         // ---- phase 3: diagonal blocks and gamma, row by row ----
         for (int base = 0; base < cnt; base += ngroups) {
@@ -372,6 +397,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
             }
         }
         __syncthreads();
+        SCHUR_MARK(3);
 
         // ---- phase 4: results ----
         copy_coalesced<T>(static_cast<T *>(a.S) + ((size_t)prob * N + k0) * BSZ, img, cnt * BSZ, false);
@@ -384,6 +410,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
             }
         }
         __syncthreads();
+        SCHUR_MARK(4);
     }
 }
 
