@@ -118,12 +118,15 @@ __device__ __forceinline__ void block_mv_bcast(const T *__restrict__ M, const T 
 // the image of the augmented identity column there: exactly the values of Gauss-Jordan on [A | I] in the arithmetic order
 // of glass::invertMatrix (reference GLASS/src/L3/inv.cuh:27-33).  All lanes of the warp must call it (__syncwarp inside);
 // lanes with valid == false compute on dummies.
+// `nsteps` (warp-uniform, <= NX): pivots to run; a block padded with an identity tail (schur_form.cuh pads R_k) needs
+// only its leading nsteps pivots -- the remaining ones would multiply by exactly 1 and subtract exactly 0.
 template <typename T, int NX, int CPL>
-__device__ __forceinline__ void gj_invert_cols(T (&col)[CPL][NX], const bool valid, const int li, T *scr)
+__device__ __forceinline__ void gj_invert_cols(T (&col)[CPL][NX], const bool valid, const int li, T *scr, const int nsteps = NX)
 {
     constexpr int V = PVec<T>::V;
 #pragma unroll
     for (int p = 0; p < NX; p++) {
+        if (p >= nsteps) break;
         if (valid && li == p / CPL) {
             const T pv_inv = (T)1 / col[p % CPL][p];
 #pragma unroll

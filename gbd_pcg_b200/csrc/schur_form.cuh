@@ -218,6 +218,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
     T *scr = scr_all + (lane_on ? group : 0) * 16;
     const int c0 = li * CPL;                                    // first column this lane owns
     const uint32_t items = a.batch * nchunks;
+    bool bulk_pending = false;
 
     for (uint32_t item = blockIdx.x; item < items; item += gridDim.x) {
         const uint32_t prob = item / nchunks;
@@ -237,6 +238,11 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
 #ifdef SCHUR_TRACE
         long long tmark_ = clock64();
 #endif
+        if (bulk_pending) {                                    // the previous item's bulk stores must have finished reading Qs / img
+            if (t == 0) pv_bulk_wait_read();
+            __syncthreads();
+            bulk_pending = false;
+        }
         // ---- phase 0: stage the chunk's data ----
         // (every piece is an asynchronous cp.async copy: all of them are in flight together, one wait)
         async_copy<T>(Qs + (size_t)i_lo * BB, Q + (size_t)knot(i_lo) * BB, (cnt + 1 - i_lo) * BB);
@@ -283,7 +289,9 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
             for (int cc = 0; cc < CPL; cc++)
 #pragma unroll
                 for (int rr = 0; rr < NX; rr++) col[cc][rr] = valid ? blk[cc * NX + rr] : ((rr == c0 + cc) ? (T)1 : (T)0);
-            gj_invert_cols<T, NX, CPL>(col, valid, li, scr);
+            // R blocks are padded with an identity tail: nu pivots suffice; the warp runs as many as its longest block needs
+            const int nsteps = __reduce_max_sync(0xffffffffu, valid ? (isR ? nu : NX) : 0);
+            gj_invert_cols<T, NX, CPL>(col, valid, li, scr, nsteps);
             if (valid) {
 #pragma unroll
                 for (int cc = 0; cc < CPL; cc++)
@@ -399,9 +407,25 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
         __syncthreads();
         SCHUR_MARK(3);
 
-        // ---- phase 4: results ----
-        copy_coalesced<T>(static_cast<T *>(a.S) + ((size_t)prob * N + k0) * BSZ, img, cnt * BSZ, false);
-        if (a.Qinv) copy_coalesced<T>(static_cast<T *>(a.Qinv) + ((size_t)prob * N + k0) * BB, Qs + BB, cnt * BB, false);
+        // ---- phase 4: results (S image and Q^-1 leave through the TMA engine when 16-byte aligned) ----
+        {
+            T *Sdst = static_cast<T *>(a.S) + ((size_t)prob * N + k0) * BSZ;
+            T *Qdst = a.Qinv ? static_cast<T *>(a.Qinv) + ((size_t)prob * N + k0) * BB : nullptr;
+            const bool bulk = (sizeof(T) * BB) % 16 == 0 && (reinterpret_cast<uintptr_t>(Sdst) & 15u) == 0 &&
+                              (reinterpret_cast<uintptr_t>(Qdst) & 15u) == 0;
+            if (bulk) {
+                pv_fence_async();          // this thread's generic-proxy writes of the image -> visible to the async proxy
+                __syncthreads();
+                if (t == 0) {
+                    pv_bulk_s2g(Sdst, pv_smem_u32(img), (uint32_t)(cnt * BSZ * (int)sizeof(T)));
+                    if (Qdst) pv_bulk_s2g(Qdst, pv_smem_u32(Qs + BB), (uint32_t)(cnt * BB * (int)sizeof(T)));
+                }
+                bulk_pending = true;
+            } else {
+                copy_coalesced<T>(Sdst, img, cnt * BSZ, false);
+                if (Qdst) copy_coalesced<T>(Qdst, Qs + BB, cnt * BB, false);
+            }
+        }
         if (a.Rinv) {
             T *Ro = static_cast<T *>(a.Rinv) + ((size_t)prob * (N - 1)) * nu * nu;
             for (int e = t; e < cnt * nu * nu; e += nthr) {
@@ -412,6 +436,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
         __syncthreads();
         SCHUR_MARK(4);
     }
+    if (bulk_pending && t == 0) pv_bulk_wait_read();           // shared memory must outlive the last bulk store
 }
 
 // x_k = -Q_k^-1 (q_k + lambda_k - A_k^T lambda_{k+1}),  u_k = -R_k^-1 (r_k - B_k^T lambda_{k+1});  one CTA per (system, k)
