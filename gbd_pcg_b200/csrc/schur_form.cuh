@@ -217,6 +217,11 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
     T *vq = scr_all + (size_t)ngroups * 16, *vr = vq + (size_t)W * NX, *vc = vr + (size_t)W * NX, *vrc = vc + (size_t)chunk * NX;
     T *scr = scr_all + (lane_on ? group : 0) * 16;
     const int c0 = li * CPL;                                    // first column this lane owns
+    // phase-3 mapping: C3 = 1 column per lane, NX lanes per block-row
+    constexpr int C3 = 1, LPB3 = NX / C3, GPW3 = 32 / LPB3;
+    const int gl3 = lane / LPB3, c3 = (lane - gl3 * LPB3) * C3;
+    const bool lane_on3 = gl3 < GPW3;
+    const int group3 = warp * GPW3 + gl3, ngroups3 = (nthr >> 5) * GPW3;
     const uint32_t items = a.batch * nchunks;
     bool bulk_pending = false;
 
@@ -342,50 +347,51 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
         __syncthreads();
         SCHUR_MARK(2);
 
-        // ---- phase 3: diagonal blocks and gamma, row by row ----
-        for (int base = 0; base < cnt; base += ngroups) {
-            const int lb = base + group;
-            const bool valid = lane_on && lb < cnt;
+        // ---- phase 3: diagonal blocks and gamma, row by row (one column per lane: a row keeps NX lanes busy, so the
+        //      chunk's rows fill the CTA in one round) ----
+        for (int base = 0; base < cnt; base += ngroups3) {
+            const int lb = base + group3;
+            const bool valid = lane_on3 && lb < cnt;
             if (!__any_sync(0xffffffffu, valid)) continue;      // warp-uniform
             const int lbv = valid ? lb : 0, j = k0 + lbv;
             const T *Qj = Qs + (size_t)(lbv + 1) * BB;
             T *row = img + (size_t)lbv * BSZ;
-            T out[CPL][NX];
+            T out[C3][NX];
 #pragma unroll
-            for (int cc = 0; cc < CPL; cc++)
+            for (int cc = 0; cc < C3; cc++)
 #pragma unroll
-                for (int rr = 0; rr < NX; rr++) out[cc][rr] = -Qj[(c0 + cc) * NX + rr];
-            T gam[CPL];
+                for (int rr = 0; rr < NX; rr++) out[cc][rr] = -Qj[(c3 + cc) * NX + rr];
+            T gam[C3];
 #pragma unroll
-            for (int cc = 0; cc < CPL; cc++) {
+            for (int cc = 0; cc < C3; cc++) {
                 T s = (T)0;
 #pragma unroll
-                for (int p = 0; p < NX; p++) s += Qj[p * NX + c0 + cc] * vq[(lbv + 1) * NX + p];
+                for (int p = 0; p < NX; p++) s += Qj[p * NX + c3 + cc] * vq[(lbv + 1) * NX + p];
                 gam[cc] = s;
             }
             if (valid && j > 0) {
-                T v[CPL][NX], w2[CPL][NX];
+                T v[C3][NX], w2[C3][NX];
 #pragma unroll
-                for (int cc = 0; cc < CPL; cc++)
+                for (int cc = 0; cc < C3; cc++)
 #pragma unroll
-                    for (int p = 0; p < NX; p++) v[cc][p] = As[(size_t)lbv * BB + p * NX + c0 + cc];       // row c0+cc of A_k
-                block_mv_bcast<T, NX, CPL>(row, v, out);                                                  // AQ A_k^T
+                    for (int p = 0; p < NX; p++) v[cc][p] = As[(size_t)lbv * BB + p * NX + c3 + cc];       // row c0+cc of A_k
+                block_mv_bcast<T, NX, C3>(row, v, out);                                                  // AQ A_k^T
 #pragma unroll
-                for (int cc = 0; cc < CPL; cc++)
+                for (int cc = 0; cc < C3; cc++)
 #pragma unroll
-                    for (int p = 0; p < NX; p++) v[cc][p] = Bs[(size_t)lbv * BB + p * NX + c0 + cc];       // row c0+cc of B_k (padded)
-                block_mv_bcast<T, NX, CPL>(row + BB, v, w2);                                              // BR B_k^T
+                    for (int p = 0; p < NX; p++) v[cc][p] = Bs[(size_t)lbv * BB + p * NX + c3 + cc];       // row c0+cc of B_k (padded)
+                block_mv_bcast<T, NX, C3>(row + BB, v, w2);                                              // BR B_k^T
 #pragma unroll
-                for (int cc = 0; cc < CPL; cc++)
+                for (int cc = 0; cc < C3; cc++)
 #pragma unroll
-                    for (int rr = 0; rr < NX; rr++) out[cc][rr] = -((out[cc][rr] + w2[cc][rr]) + Qj[(c0 + cc) * NX + rr]);
+                    for (int rr = 0; rr < NX; rr++) out[cc][rr] = -((out[cc][rr] + w2[cc][rr]) + Qj[(c3 + cc) * NX + rr]);
 #pragma unroll
-                for (int cc = 0; cc < CPL; cc++) {
+                for (int cc = 0; cc < C3; cc++) {
                     T s1 = (T)0, s2 = (T)0;
 #pragma unroll
                     for (int p = 0; p < NX; p++) {
-                        s1 += row[p * NX + c0 + cc] * vq[lbv * NX + p];
-                        s2 += row[BB + p * NX + c0 + cc] * vr[lbv * NX + p];
+                        s1 += row[p * NX + c3 + cc] * vq[lbv * NX + p];
+                        s2 += row[BB + p * NX + c3 + cc] * vr[lbv * NX + p];
                     }
                     gam[cc] = (gam[cc] - s1) - s2;
                 }
@@ -393,14 +399,14 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 2 : 1)) schur_form_nx_k
             __syncwarp();          // BR (parked in the diagonal slot) has been read by the whole group
             if (valid) {
 #pragma unroll
-                for (int cc = 0; cc < CPL; cc++) {
+                for (int cc = 0; cc < C3; cc++) {
 #pragma unroll
                     for (int rr = 0; rr < NX; rr++) {
-                        row[BB + (c0 + cc) * NX + rr] = out[cc][rr];
-                        if (j == 0) row[(c0 + cc) * NX + rr] = (T)0;
-                        if (j == N - 1) row[2 * BB + (c0 + cc) * NX + rr] = (T)0;
+                        row[BB + (c3 + cc) * NX + rr] = out[cc][rr];
+                        if (j == 0) row[(c3 + cc) * NX + rr] = (T)0;
+                        if (j == N - 1) row[2 * BB + (c3 + cc) * NX + rr] = (T)0;
                     }
-                    static_cast<T *>(a.gamma)[((size_t)prob * N + j) * NX + c0 + cc] = gam[cc] - vc[lbv * NX + c0 + cc];
+                    static_cast<T *>(a.gamma)[((size_t)prob * N + j) * NX + c3 + cc] = gam[cc] - vc[lbv * NX + c3 + cc];
                 }
             }
         }
