@@ -269,6 +269,37 @@ def run_ours(args):
     build_ms = statistics.median(a.elapsed_time(b) for a, b in evb)
     build_err = float((d_Pb - d_P).abs().max().item() / d_P.abs().max().item())
     del d_Pb
+
+    # ---- the whole device-resident MPC step: stage data -> S, gamma -> stair Phi^-1 -> PCG -> (x, u) ----
+    mpc = None
+    if rank == 0:
+        nseed = 16
+        sd = [g.synth.lqr_stage_data(NX, NU, N_KNOT, s_, dtype=DTYPE) for s_ in range(nseed)]
+        dd = {k: torch.from_numpy(np.concatenate([d_[k] for d_ in sd])).cuda().repeat(batch // nseed, 1).contiguous() for k in sd[0]}
+        f32 = dict(dtype=torch.float32, device="cuda")
+        mS, mg = torch.empty(batch * 3 * N_KNOT * NX * NX, **f32), torch.empty(batch * N_KNOT * NX, **f32)
+        mP, ml = torch.empty_like(mS), torch.zeros(batch * N_KNOT * NX, **f32)
+        mQi, mRi = torch.empty(batch * N_KNOT * NX * NX, **f32), torch.empty(batch * (N_KNOT - 1) * NU * NU, **f32)
+        mx, mu = torch.empty(batch * N_KNOT * NX, **f32), torch.empty(batch * (N_KNOT - 1) * NU, **f32)
+        stages = [("schur_form_ms", lambda: g.schur_form_dev(NX, NU, N_KNOT, batch, dd["Q"], dd["R"], dd["A"], dd["B"], dd["q"], dd["r"], dd["c"],
+                                                             mS, mg, mQi, mRi)),
+                  ("build_pinv_ms", lambda: g.build_pinv_dev(NX, N_KNOT, batch, mS, mP, "stair")),
+                  ("pcg_ms", lambda: (ml.zero_(), g.solve_batched_dev(NX, N_KNOT, batch, mS, mP, mg, ml, cfg, d_it, d_ex))),
+                  ("recover_ms", lambda: g.schur_recover_dev(NX, NU, N_KNOT, batch, mQi, mRi, dd["A"], dd["B"], dd["q"], dd["r"], ml, mx, mu))]
+        mpc = {}
+        for name, fn in stages:
+            ts = []
+            for i_ in range(8):
+                torch.cuda._sleep(200000)
+                ea, eb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                ea.record(); fn(); eb.record()
+                torch.cuda.synchronize()
+                if i_ >= 3:
+                    ts.append(ea.elapsed_time(eb))
+            mpc[name] = statistics.median(ts)
+        mpc["steps_per_s"] = batch / (sum(mpc.values()) * 1e-3)
+        mpc["note"] = "gbdpcg_schur_form_dev + build_pinv_dev(stair) + solve_batched_dev + schur_recover_dev on the resident batch"
+        del dd, mS, mg, mP, ml, mQi, mRi, mx, mu
     for p in (pS, pP, pg, pl):
         lib.gbdpcg_host_free(p)
 
@@ -358,6 +389,7 @@ def run_ours(args):
                     "lambda_max_diff_vs_host_pinv": lam_err},
             "pinv_build": {"ms": build_ms, "gb_per_s": 2 * S.nbytes / build_ms / 1e6, "max_rel_diff_vs_fp64_host_build": build_err,
                            "note": "gbdpcg_build_pinv_dev_f32 (stair) on the resident batch: reads S, writes Phi^-1"},
+            "mpc_step": mpc,
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": measured_traffic(batch), "algorithmic_bytes_per_launch": bytes_per_solve * batch,
