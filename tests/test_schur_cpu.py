@@ -56,3 +56,31 @@ def test_whole_chain_on_the_host():
     z = np.linalg.solve(K, np.concatenate([-gg, -c]))[:G.shape[0]]
     zz = np.concatenate([np.concatenate([x[k * nx:(k + 1) * nx], u[k * nu:(k + 1) * nu]]) for k in range(N)])
     assert np.abs(zz - z).max() < 1e-6 * np.abs(z).max()
+
+
+def example_stage_data(dt=np.float64):
+    """The pendulum LQR the reference example's literal S decodes to (examples/pcg_solve.cu:14-22):
+    A = [[1, 0.1], [-0.981, 1]], B = [0, 0.1]^T, Q^-1 = 0.999 I, R^-1 = 9.9, Q_N^-1 = 0.01 I, N = 3."""
+    nx, nu, N = 2, 1, 3
+    A = np.array([[1.0, 0.1], [-0.981, 1.0]])
+    B = np.array([[0.0], [0.1]])
+    cm = lambda Ms: np.stack([np.ascontiguousarray(M.T).reshape(-1) for M in Ms]).astype(dt)
+    Q = [np.eye(2) / 0.999, np.eye(2) / 0.999, np.eye(2) / 0.01]
+    return {"Q": cm(Q), "R": cm([np.eye(1) / 9.9] * 2), "A": cm([A, A]), "B": cm([B, B]),
+            "q": np.zeros((N, nx), dt), "r": np.zeros((N - 1, nu), dt), "c": np.zeros((N, nx), dt)}, nx, nu, N
+
+
+def test_reference_example_matrix_is_the_schur_complement_of_its_pendulum():
+    """Known answer from the reference's own input: forming S from the decoded stage data reproduces the 36 literal
+    numbers of examples/pcg_solve.cu:14-22 to the 4 digits they are printed with."""
+    d, nx, nu, N = example_stage_data()
+    S, gam, _, _ = oracle.schur_form(*FLAT(d), nx, nu, N)
+    assert np.abs(S - g.synth.EXAMPLE_S).max() < 6e-5
+    assert not gam.any()                                        # q = r = c = 0
+
+
+def test_example_preconditioners_known_answer():
+    """Phi^-1 of the reference example's S: oracle Gauss-Jordan against numpy.linalg.inv (synth.example_system)."""
+    for kind in ("jacobi", "stair"):
+        S, P, _ = g.synth.example_system(np.float64, kind)
+        assert np.abs(oracle.build_pinv(S, 2, 3, kind) - P).max() < 1e-13

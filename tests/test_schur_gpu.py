@@ -106,3 +106,17 @@ def test_resident_chain_against_the_kkt_solution(dt, tol, zbar):
         assert rel_err(zz, z) < zbar
     for i in range(4, B):
         assert np.array_equal(xs[i], xs[i % 4]) and np.array_equal(us[i], us[i % 4])
+
+
+def test_reference_example_matrix_from_its_stage_data():
+    """GPU formation of the pendulum LQR the reference example decodes to reproduces examples/pcg_solve.cu:14-22 (fp32 and fp64)."""
+    torch = _torch()
+    from test_schur_cpu import example_stage_data
+    for dt in (np.float32, np.float64):
+        d, nx, nu, N = example_stage_data(dt)
+        dd = to_dev(d)
+        S = torch.empty(3 * N * nx * nx, dtype=dd["Q"].dtype, device="cuda")
+        gam = torch.empty(N * nx, dtype=S.dtype, device="cuda")
+        g.schur_form_dev(nx, nu, N, 1, dd["Q"], dd["R"], dd["A"], dd["B"], dd["q"], dd["r"], dd["c"], S, gam)
+        torch.cuda.synchronize()
+        assert np.abs(S.cpu().numpy().astype(np.float64) - g.synth.EXAMPLE_S).max() < 6e-5
