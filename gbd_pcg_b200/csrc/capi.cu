@@ -102,7 +102,7 @@ template <typename T>
 static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
 {
     constexpr bool f64 = sizeof(T) == 8;
-    int fused = f64 ? 0 : 1;                                   // default recurrence per dtype
+    int fused = 1;                                             // single-reduction recurrence unless asked otherwise (parity measured per dtype)
     if (cfg.flags & GBDPCG_FLAG_TEXTBOOK) fused = 0;
     if (cfg.flags & GBDPCG_FLAG_FUSED) fused = 1;
     const FusedVariant *tab;

@@ -10,13 +10,13 @@
 // What the reference does per iteration (include/pcg.cuh:154-208): 2 block-row mat-vecs through shared
 // memory with nx of 64 threads working, 2 grid-wide dot products (global partials + grid.sync +
 // redundant re-reduction), 4 grid.sync.  What this kernel does per iteration:
-//   FUSED = true  (default for fp32): Chronopoulos-Gear form of the same recurrence -- r~ = Phi^-1 r and
+//   FUSED = true  (the default): Chronopoulos-Gear form of the same recurrence -- r~ = Phi^-1 r and
 //       w = S r~ are formed first, then gamma = r.r~ and delta = w.r~ are reduced TOGETHER, and
 //       beta = gamma/gamma_old, alpha = gamma/(delta - beta*gamma/alpha_old), p = r~ + beta p,
 //       s = w + beta s (= S p), lambda += alpha p, r -= alpha s.  Same iterates in exact arithmetic, same
 //       exit test on the same quantity (|r.Phi^-1 r| < tol after each update), ONE reduction and three
 //       block barriers per iteration.
-//   FUSED = false (default for fp64, or GBDPCG_FLAG_TEXTBOOK): the reference's own order of operations
+//   FUSED = false (GBDPCG_FLAG_TEXTBOOK): the reference's own order of operations
 //       (two reductions, four barriers).
 // Reductions are warp shuffles + one shared-memory hop (+ one DSMEM hop per CTA in cluster mode); every
 // thread re-sums the same partials in the same order, so alpha, beta and the exit decision are

@@ -62,10 +62,9 @@ typedef struct gbdpcg_config {
 #define GBDPCG_FLAG_FORCE_GENERIC 0x1u /* use the runtime-nx fallback kernel even if a specialised one exists */
 #define GBDPCG_FLAG_PINV_SMEM 0x2u     /* keep Phi^-1 rows in shared memory instead of registers              */
 #define GBDPCG_FLAG_PINV_REG 0x4u      /* keep Phi^-1 rows in registers (fail if they do not fit)             */
-#define GBDPCG_FLAG_TEXTBOOK 0x8u      /* the reference's order of operations: two reductions per iteration
-                                          (default for fp64)                                                  */
+#define GBDPCG_FLAG_TEXTBOOK 0x8u      /* the reference's order of operations: two reductions per iteration */
 #define GBDPCG_FLAG_FUSED 0x10u        /* single-reduction (Chronopoulos-Gear) form of the same recurrence
-                                          (default for fp32)                                                  */
+                                          (the default for both precisions)                                   */
 #define GBDPCG_FLAG_LEGACY_ROWS 0x20u  /* first-generation one-row-per-thread kernel (kept for A/B measurements) */
 #define GBDPCG_FLAG_SLAB_LAYOUT 0x80u  /* fp32: column-slab ownership of the matrix entries (pcg_slab.cuh); fewer shared-memory
                                           bytes per mat-vec, more instructions -- measured slower on C2, kept for A/B */

@@ -393,7 +393,7 @@ def test_cpp_examples_run(example, iters, tmp_path):
 # kernel-selection flags: every recurrence / staging / generation variant solves the same systems
 # ---------------------------------------------------------------------------------------------
 @pytest.mark.parametrize("flag", ["TEXTBOOK", "FUSED", "NO_TMA", "LEGACY_ROWS", "SLAB_LAYOUT"])
-@pytest.mark.parametrize("name,precond", [("C2", "stair"), ("C2", "identity"), ("C3", "stair"), ("C4", "jacobi")])
+@pytest.mark.parametrize("name,precond", [("C2", "stair"), ("C2", "identity"), ("C3", "stair"), ("C3", "identity"), ("C4", "jacobi")])
 def test_kernel_variant_flags(flag, name, precond):
     S, P, gam, nx, N, tol, max_iter = make_system(name, precond)
     lam0 = np.zeros(N * nx, dtype=S.dtype)
