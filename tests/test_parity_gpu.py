@@ -160,6 +160,36 @@ def test_c4_cluster16_registers_and_cluster8_smem():
         check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex)
 
 
+def _largest_plannable_N(nx, dt):
+    lo, hi = 2, 1 << 18
+    while lo < hi:
+        mid = (lo + hi + 1) // 2
+        try:
+            g.plan_query(nx, mid, dt, True)
+            lo = mid
+        except g.GbdpcgError:
+            hi = mid - 1
+    return lo
+
+
+@pytest.mark.parametrize("nx,nu,dt", [(14, 7, np.float32), (14, 7, np.float64), (16, 8, np.float32), (2, 1, np.float32), (8, 4, np.float64)])
+def test_maximum_knot_points(nx, nu, dt):
+    """The largest system the planner accepts for this state size (16-CTA clusters, or the one-CTA run-time kernel):
+    solved to the bar; one knot point more is refused with GBDPCG_ERR_UNSUPPORTED, never mis-solved."""
+    N = _largest_plannable_N(nx, dt)
+    assert N >= 256
+    tol = 1e-6 if dt == np.float32 else 1e-10
+    S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 4000), "stair", seed=5)
+    lam0 = np.zeros(N * nx, dtype=dt)
+    lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
+    assert not ex
+    check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex, noise_floor=True)
+    S2, P2, gam2, _, N2, _, _ = make_system((nx, nu, N + 1, dt, tol, 4000), "stair", seed=5)
+    with pytest.raises(g.GbdpcgError) as e:
+        gpu_solve(S2, P2, gam2, np.zeros(N2 * nx, dtype=dt), nx, N2, tol, max_iter)
+    assert e.value.status == g._lib.ERR_UNSUPPORTED
+
+
 # ---------------------------------------------------------------------------------------------
 # semantics the reference defines (SURVEY App. A.1)
 # ---------------------------------------------------------------------------------------------
