@@ -93,6 +93,12 @@ static void fused_variants(bool f64, int nx, int fused, const FusedVariant **tab
         break;
         GBDPCG_FOR_EACH_NX(CASE)
 #undef CASE
+#define CASE(NX)                                                                                                       \
+    case NX:                                                                                                           \
+        if (fused) *tab = f64 ? fused_variants_f64_##NX##_1(cnt) : fused_variants_f32_##NX##_1(cnt);                   \
+        break;
+        GBDPCG_FOR_EACH_NX_EXTRA(CASE)
+#undef CASE
         default: break;
     }
 }
@@ -274,7 +280,9 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
     a.N = N; a.batch = batch; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg.max_iter; a.two_buffers = (p.nbuf == 2);
     if (p.fused_kernel) {
         // field reused as the TMA switch: bulk copies need 16-byte aligned sources (strides are multiples of 16 for even nx)
-        const bool aligned = ((uintptr_t)S % 16 == 0) && (!P || (uintptr_t)P % 16 == 0) && ((a.mat_stride * sizeof(T)) % 16 == 0);
+        // (odd nx: a block-row is not a multiple of 16 bytes, so a CTA's share of the matrix is not bulk-copyable)
+        const bool aligned = ((uintptr_t)S % 16 == 0) && (!P || (uintptr_t)P % 16 == 0) && ((a.mat_stride * sizeof(T)) % 16 == 0) &&
+                             ((3ull * nx * nx * sizeof(T)) % 16 == 0);
         a.two_buffers = (aligned && p.pmode != P_SMEM && !(cfg.flags & GBDPCG_FLAG_NO_TMA)) ? 1u : 0u;
     }
     a.tol = (T)cfg.exit_tol;

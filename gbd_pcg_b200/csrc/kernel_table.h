@@ -19,6 +19,10 @@ struct RowsVariant {
 
 // State sizes with a specialised kernel.  Keep in sync with NX_LIST in csrc/Makefile.
 #define GBDPCG_FOR_EACH_NX(X) X(2) X(4) X(6) X(8) X(10) X(12) X(14) X(16)
+// State sizes that get the fused solver kernel only, in its default single-reduction recurrence (no column-slab or
+// first-generation variants, and the preconditioner builder / Schur kernels use their run-time-nx form): odd sizes
+// run one row per thread, sizes above 16 keep Phi^-1 in shared memory.  Keep in sync with NX_EXTRA in the Makefile.
+#define GBDPCG_FOR_EACH_NX_EXTRA(X) X(3) X(5) X(7) X(9) X(11) X(13) X(15) X(18) X(20) X(22) X(24) X(28) X(32)
 
 #define GBDPCG_DECLARE_TABLE(NX)                               \
     const RowsVariant *rows_variants_f32_##NX(int *count);     \
@@ -47,5 +51,10 @@ struct FusedVariant {
     const FusedVariant *fused_variants_f64_##NX##_1(int *count);
 GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_FUSED)
 #undef GBDPCG_DECLARE_FUSED
+#define GBDPCG_DECLARE_FUSED_EXTRA(NX)                             \
+    const FusedVariant *fused_variants_f32_##NX##_1(int *count);   \
+    const FusedVariant *fused_variants_f64_##NX##_1(int *count);
+GBDPCG_FOR_EACH_NX_EXTRA(GBDPCG_DECLARE_FUSED_EXTRA)
+#undef GBDPCG_DECLARE_FUSED_EXTRA
 
 }  // namespace gbdpcg

@@ -1,5 +1,5 @@
 // pcg_fused_inst.cu -- instantiates the fused kernel (pcg_fused.cuh) for one (dtype, nx, recurrence); compiled
-// once per triple with  -DINST_NX=<nx> -DINST_F64=<0|1> -DINST_FUSED=<0|1>   (see csrc/Makefile)
+// once per triple with  -DINST_NX=<nx> -DINST_F64=<0|1> -DINST_FUSED=<0|1> [-DINST_NO_SLAB]   (see csrc/Makefile)
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
 #include "pcg_slab.cuh"
@@ -17,7 +17,11 @@ typedef double InstT;
 #else
 typedef float InstT;
 #define INST_DT "f32"
+#if INST_NX % 2
+#define INST_RPT 1       // odd state size: one row per thread
+#else
 #define INST_RPT 2       // two rows per thread: window loads, shuffles and scalar work are shared by both rows
+#endif
 #endif
 #define CAT4_(a, b, c, d) a##b##_##c##_##d
 #define CAT4(a, b, c, d) CAT4_(a, b, c, d)
@@ -75,7 +79,7 @@ constexpr int SMAXT_2K = SMAXT_2 > 32 ? SMAXT_2 : 32;
      "pcg_slab<" INST_DT ",nx=" STR(INST_NX) "," #CL "," #PM "," STR(INST_FUSED) ">"}
 
 static const FusedVariant g_table[] = {
-#if !INST_F64
+#if !INST_F64 && !defined(INST_NO_SLAB)
     // selected only with GBDPCG_FLAG_SLAB_LAYOUT
     SLAB_VARIANT(0, P_NONE, SMAXT_1), SLAB_VARIANT(1, P_NONE, SMAXT_1),
     SLAB_VARIANT(0, P_REG, SMAXT_2K), SLAB_VARIANT(1, P_REG, SMAXT_2K),
@@ -87,8 +91,9 @@ static const FusedVariant g_table[] = {
 
 const FusedVariant *INST_TABLE_NAME(int *count)
 {
-    // the row-layout P_REG entries are the last two; dropped when they cannot fit the register file
-    *count = (int)(sizeof g_table / sizeof g_table[0]) - ((MAXT_2 > 0) ? 0 : 2);
+    // the row-layout P_REG entries are the last two; dropped when they cannot fit the register file.  A state size whose
+    // S rows alone overflow it has no usable entry at all (the planner then takes the run-time-nx kernel).
+    *count = (maxt_for(NX, 1) > 0) ? (int)(sizeof g_table / sizeof g_table[0]) - ((MAXT_2 > 0) ? 0 : 2) : 0;
     return g_table;
 }
 

@@ -27,7 +27,9 @@ def p50(launch, d_l, n_warm=10, n=100):
     return ts[len(ts) // 2]
 
 
-for shape in ("C2", "C3", "C4", (20, 10, 32, np.float32, 1e-6, 2000), (24, 12, 64, np.float32, 1e-6, 2000), (32, 16, 32, np.float64, 1e-10, 2000)):
+for shape in ("C2", "C3", "C4", (18, 9, 32, np.float32, 1e-6, 2000), (20, 10, 32, np.float32, 1e-6, 2000), (20, 10, 32, np.float64, 1e-10, 2000),
+              (24, 12, 64, np.float32, 1e-6, 2000), (24, 12, 64, np.float64, 1e-10, 2000), (28, 14, 100, np.float32, 1e-6, 2000), (32, 16, 32, np.float32, 1e-6, 2000),
+              (32, 16, 32, np.float64, 1e-10, 2000)):
     S, P, gam, nx, N, tol, max_iter = make_system(shape, "stair")
     d = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
     d_S, d_P, d_g = d(S), d(P), d(gam)

@@ -7,7 +7,7 @@ import pytest
 
 import gbd_pcg_b200 as g
 from conftest import GOLDEN, LAMBDA_TOL, rel_err
-from helpers import PRECONDS, make_system, oracle_at_iters
+from helpers import random_block_tridiagonal, PRECONDS, make_system, oracle_at_iters
 from oracle import oracle
 
 pytestmark = pytest.mark.gpu
@@ -95,34 +95,41 @@ def test_other_shapes_vs_oracle(shape, precond):
     check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex, noise_floor=True)
 
 
-@pytest.mark.parametrize("shape", [(3, 1, 3, np.float32, 1e-6, 100), (5, 2, 12, np.float64, 1e-10, 300),
-                                   (7, 3, 30, np.float32, 1e-6, 300), (14, 7, 32, np.float32, 1e-6, 1000)])
+EXTRA_SHAPES = [(3, 3), (3, 700), (5, 12), (7, 30), (9, 33), (11, 100), (13, 64), (15, 64), (15, 250), (18, 32), (20, 32), (22, 50), (24, 64),
+                (28, 100), (32, 32)]
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("precond", ["identity", "jacobi", "stair"])
+@pytest.mark.parametrize("nx,N", EXTRA_SHAPES)
+def test_odd_and_large_state_sizes_vs_oracle(nx, N, precond, dt):
+    """State sizes beyond the even 2..16 set: odd ones (one row per thread, no bulk copies: a block-row is not a multiple
+    of 16 bytes) and 18..32 (Phi^-1 resident in shared memory, clusters) run the specialised kernel too."""
+    if nx % 2:
+        S, P, gam = random_block_tridiagonal(nx, N, precond, dt, seed=nx + N, coupled=True)
+    else:
+        S, P, gam = g.synth.lqr_schur(nx, nx // 2, N, 2, precond, dt)
+        P = None if precond == "identity" else P
+    tol, max_iter = (1e-6 if dt == np.float32 else 1e-10), 3000
+    info = g.plan_query(nx, N, dt, P is not None)
+    assert info["specialised"] == (0 if (nx > 24 and dt == np.float64) else 1), info
+    lam0 = np.zeros(N * nx, dtype=dt)
+    lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
+    assert not ex
+    check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex, noise_floor=True)
+
+
+@pytest.mark.parametrize("shape", [(3, 1, 3, np.float32, 1e-6, 100), (5, 2, 12, np.float64, 1e-10, 300), (17, 0, 20, np.float32, 1e-6, 300),
+                                   (7, 3, 30, np.float32, 1e-6, 300), (14, 7, 32, np.float32, 1e-6, 1000), (19, 0, 40, np.float64, 1e-10, 300)])
 @pytest.mark.parametrize("precond", ["identity", "stair"])
 def test_generic_fallback_vs_oracle(shape, precond):
-    """Runtime-nx kernel: odd state sizes (no specialised instantiation) and the forced-generic flag."""
+    """Runtime-nx kernel (state sizes without an instantiation, e.g. 17, take it by themselves): forced here by flag."""
     nx, nu, N, dt, tol, max_iter = shape
     if nx % 2:
-        # the generator needs an even nx; build an odd-nx system from dense random SPD blocks instead
-        rng = np.random.default_rng(11)
-        n = nx * N
-        A = np.zeros((n, n))
-        for k in range(N):
-            M = rng.standard_normal((nx, nx))
-            A[k*nx:(k+1)*nx, k*nx:(k+1)*nx] = -(M @ M.T + 4 * nx * np.eye(nx))
-            if k + 1 < N:
-                L = rng.standard_normal((nx, nx))
-                A[(k+1)*nx:(k+2)*nx, k*nx:(k+1)*nx] = L
-                A[k*nx:(k+1)*nx, (k+1)*nx:(k+2)*nx] = L.T
-        S = g.layout.pack_dense(A, nx, N).astype(dt)
-        diag = np.stack([A[k*nx:(k+1)*nx, k*nx:(k+1)*nx] for k in range(N)])
-        lower = np.stack([A[(k+1)*nx:(k+2)*nx, k*nx:(k+1)*nx] for k in range(N - 1)])
-        pd, pl = g.synth.preconditioner_blocks(diag, lower, precond)
-        P = None if precond == "identity" else g.layout.pack_blocks(pd, pl).astype(dt)
-        gam = rng.standard_normal(n).astype(dt)
-        flags = 0
+        S, P, gam = random_block_tridiagonal(nx, N, precond, dt)
     else:
         S, P, gam, nx, N, tol, max_iter = make_system(shape, precond)
-        flags = g._lib.FLAG_FORCE_GENERIC
+    flags = g._lib.FLAG_FORCE_GENERIC
     assert g.plan_query(nx, N, dt, P is not None, g.pcg_config(flags=flags))["specialised"] == 0
     lam0 = np.zeros(N * nx, dtype=dt)
     lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter, flags=flags)
@@ -301,6 +308,39 @@ def test_batched_equals_single_and_oracle(shape, batch):
         assert (its[idx] == it1).all()
         assert all(np.array_equal(lam[i], lam1) for i in idx), "batched result differs from the single solve"
         check_against_oracle(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, lam1, it1, False)
+
+
+@pytest.mark.parametrize("nx,N,dt,batch", [(7, 30, np.float32, 400), (9, 33, np.float64, 150), (15, 64, np.float32, 90), (20, 32, np.float32, 200),
+                                           (24, 40, np.float64, 60)])
+def test_batched_odd_and_large_state_sizes(nx, N, dt, batch):
+    """The persistent batch loop on the paths the even 2..16 sizes never take: cooperative staging (odd nx: no bulk copies),
+    clusters with Phi^-1 resident in shared memory (nx > 16)."""
+    torch = _torch()
+    nseed = 5
+    tol, max_iter = (1e-6 if dt == np.float32 else 1e-10), 3000
+    if nx % 2:
+        sys_ = [random_block_tridiagonal(nx, N, "stair", dt, seed=100 + s, coupled=True) for s in range(nseed)]
+        S, P, gam = (np.stack([t[i] for t in sys_]) for i in range(3))
+    else:
+        S, P, gam = g.synth.lqr_schur_batch(nx, nx // 2, N, range(nseed), "stair", dt)
+    reps = (batch + nseed - 1) // nseed
+    d = lambda a: torch.from_numpy(np.tile(a, (reps, 1))[:batch].copy()).cuda()
+    d_S, d_P, d_g = d(S), d(P), d(gam)
+    d_l = torch.zeros(batch, N * nx, dtype=d_S.dtype, device="cuda")
+    d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+    d_ex = torch.ones(batch, dtype=torch.uint8, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0)
+    assert g.plan_query(nx, N, dt, True, cfg)["specialised"] == 1
+    g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
+    torch.cuda.synchronize()
+    lam, its, exs = d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
+    assert not exs.any()
+    for s in range(nseed):
+        lam1, it1, ex1 = gpu_solve(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter)
+        idx = np.arange(s, batch, nseed)
+        assert (its[idx] == it1).all()
+        assert all(np.array_equal(lam[i], lam1) for i in idx), "batched result differs from the single solve"
+        check_against_oracle(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, lam1, it1, ex1, noise_floor=True)
 
 
 def test_batched_host_entry_point():
