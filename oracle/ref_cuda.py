@@ -49,6 +49,9 @@ class RefKernel:
         vp = C.c_void_p
         L.ref_kernel_launch.restype = C.c_int
         L.ref_kernel_launch.argtypes = [vp] * 10 + [C.c_uint32, C.c_double, C.c_uint64]
+        if hasattr(L, "ref_kernel_launch_stream"):
+            L.ref_kernel_launch_stream.restype = C.c_int
+            L.ref_kernel_launch_stream.argtypes = [vp] * 10 + [C.c_uint32, C.c_double, C.c_uint64, vp]
         L.ref_solve_dev.restype = C.c_uint32
         L.ref_solve_dev.argtypes = [vp] * 8 + [C.c_uint32, C.c_double]
         L.ref_solve_host.restype = C.c_uint32
@@ -78,6 +81,22 @@ class RefKernel:
         e = self.L.ref_kernel_launch(self._p(d_S), self._p(d_Pinv), self._p(d_gamma), self._p(d_lambda), self._p(self.d_r),
                                      self._p(self.d_p), self._p(self.d_v), self._p(self.d_eta), self._p(self.d_iters),
                                      self._p(self.d_exit), int(max_iter), float(tol), int(self.extra_smem))
+        if e != 0:
+            raise RuntimeError(f"reference cooperative launch failed: cudaError {e}")
+
+    def make_lane(self, stream):
+        """A stream with its own scratch vectors and result scalars, for launch_on()."""
+        t, n = self.torch, self.nx * self.N
+        z = lambda k, dt: t.zeros(k, dtype=dt, device="cuda")
+        return {"stream": stream, "r": z(n, self.tdtype), "p": z(n, self.tdtype), "v": z(self.N, self.tdtype),
+                "eta": z(self.N, self.tdtype), "iters": z(1, t.int32), "exit": z(1, t.uint8)}
+
+    def launch_on(self, lane, d_S, d_Pinv, d_gamma, d_lambda, max_iter, tol):
+        """The same cooperative launch on lane['stream'] (several solves in flight; not something the reference API offers)."""
+        e = self.L.ref_kernel_launch_stream(self._p(d_S), self._p(d_Pinv), self._p(d_gamma), self._p(d_lambda), self._p(lane["r"]),
+                                            self._p(lane["p"]), self._p(lane["v"]), self._p(lane["eta"]), self._p(lane["iters"]),
+                                            self._p(lane["exit"]), int(max_iter), float(tol), int(self.extra_smem),
+                                            C.c_void_p(lane["stream"].cuda_stream))
         if e != 0:
             raise RuntimeError(f"reference cooperative launch failed: cudaError {e}")
 

@@ -58,6 +58,23 @@ int ref_kernel_launch(void *d_S, void *d_Pinv, void *d_gamma, void *d_lambda, vo
     return (int)e;
 }
 
+/* Same launch on a caller-chosen stream with caller-owned scratch: lets the bench keep several reference solves in
+ * flight at once (the reference's own entry points use the legacy default stream only, include/interface.cuh:132). */
+int ref_kernel_launch_stream(void *d_S, void *d_Pinv, void *d_gamma, void *d_lambda, void *d_r, void *d_p,
+                             void *d_v_temp, void *d_eta_new_temp, uint32_t *d_iters, bool *d_exit,
+                             uint32_t max_iter, double exit_tol, uint64_t extra_smem, void *stream)
+{
+    void *kernel = (void *)pcg<T, STATE_SIZE, KNOT_POINTS>;
+    T tol = (T)exit_tol;
+    void *args[] = {&d_S, &d_Pinv, &d_gamma, &d_lambda, &d_r, &d_p, &d_v_temp, &d_eta_new_temp,
+                    &d_iters, &d_exit, &max_iter, &tol};
+    size_t smem = pcgSharedMemSize<T>(STATE_SIZE, KNOT_POINTS) + extra_smem;
+    cudaError_t e = cudaLaunchCooperativeKernel(kernel, dim3(KNOT_POINTS), pcg_constants::DEFAULT_BLOCK, args, smem,
+                                                (cudaStream_t)stream);
+    if (e == cudaSuccess) e = cudaPeekAtLastError();
+    return (int)e;
+}
+
 /* Scope D.  Blocking (the reference reads the iteration count back with cudaMemcpy). */
 uint32_t ref_solve_dev(void *d_S, void *d_Pinv, void *d_gamma, void *d_lambda, void *d_r, void *d_p,
                        void *d_v_temp, void *d_eta_new_temp, uint32_t max_iter, double exit_tol)
