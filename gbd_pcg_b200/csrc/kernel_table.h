@@ -21,8 +21,10 @@ struct RowsVariant {
 #define GBDPCG_FOR_EACH_NX(X) X(2) X(4) X(6) X(8) X(10) X(12) X(14) X(16)
 // State sizes that get the fused solver kernel only, in its default single-reduction recurrence (no column-slab or
 // first-generation variants, and the preconditioner builder / Schur kernels use their run-time-nx form): odd sizes
-// run one row per thread, sizes above 16 keep Phi^-1 in shared memory.  Keep in sync with NX_EXTRA in the Makefile.
-#define GBDPCG_FOR_EACH_NX_EXTRA(X) X(3) X(5) X(7) X(9) X(11) X(13) X(15) X(18) X(20) X(22) X(24) X(28) X(32)
+// run one row per thread, sizes above 16 keep Phi^-1 in shared memory (fp64: up to 25, above that a row of S alone
+// overflows the register file and the table comes back empty).  Keep in sync with NX_EXTRA in the Makefile.
+#define GBDPCG_FOR_EACH_NX_EXTRA(X) \
+    X(3) X(5) X(7) X(9) X(11) X(13) X(15) X(17) X(18) X(19) X(20) X(21) X(22) X(23) X(24) X(25) X(26) X(27) X(28) X(29) X(30) X(31) X(32)
 
 #define GBDPCG_DECLARE_TABLE(NX)                               \
     const RowsVariant *rows_variants_f32_##NX(int *count);     \
