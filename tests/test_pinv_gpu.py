@@ -141,6 +141,31 @@ def test_host_solve_with_device_built_preconditioner(name, kind):
         assert rel_err(lam_b, lam_o) < (1e-5 if S.dtype == np.float32 else 1e-10)
 
 
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("nx,N", [(7, 30), (15, 64), (20, 32), (27, 20), (32, 32), (33, 12), (40, 8)])
+def test_host_signature_on_odd_large_and_uninstantiated_state_sizes(nx, N, dt):
+    """The reference's host signature end to end (run-time-nx builder, then whichever solver kernel the planner picks) on
+    state sizes outside the even 2..16 set, against the oracle with the oracle-built stair preconditioner."""
+    from helpers import random_block_tridiagonal
+    if nx % 2:
+        S, _, gam = random_block_tridiagonal(nx, N, "identity", dt, seed=nx, coupled=True)
+    else:
+        S, _, gam = g.synth.lqr_schur(nx, nx // 2, N, 1, "identity", dt)
+    tol, max_iter = (1e-6 if dt == np.float32 else 1e-10), 3000
+    lam = np.zeros(N * nx, dtype=dt)
+    before = g.kernel_launches()
+    it = g.solvePCG(S, gam, lam, nx, N, g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0))
+    assert g.kernel_launches() == before + 2                 # builder + solver
+    Po = oracle.build_pinv(S, nx, N, "stair")
+    lam_o, it_o, ex_o = oracle.pcg(S, Po, gam, np.zeros(N * nx, dt), nx, N, tol, max_iter)
+    assert not ex_o and abs(it - it_o) <= 1
+    if it != it_o:
+        lam_o = oracle.pcg(S, Po, gam, np.zeros(N * nx, dt), nx, N, 0.0, it)[0]
+    lam_1 = oracle.pcg(S, Po, gam, np.zeros(N * nx, dt), nx, N, 0.0, it, order=1)[0]
+    bar = max(1e-5 if dt == np.float32 else 1e-10, 3 * rel_err(lam_1, lam_o))
+    assert rel_err(lam, lam_o) < bar
+
+
 def test_batched_host_solve_with_device_built_preconditioner():
     nx, nu, N, B = 14, 7, 32, 600
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(16), "stair", np.float32)
