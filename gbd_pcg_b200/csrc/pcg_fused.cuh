@@ -44,6 +44,14 @@
 #ifndef FUSED_QBUF
 #define FUSED_QBUF 2
 #endif
+#ifndef FUSED_GHOST
+#define FUSED_GHOST 1     // cluster mode, single-reduction recurrence: neighbours' boundary block-rows of r are kept as ghost
+                          // copies (updated locally from w, alpha, beta) instead of being exchanged -> one cluster barrier less
+#endif
+#ifndef FUSED_PUSH
+#define FUSED_PUSH 1      // cluster mode with ghost copies: halo rows and reduction partials travel as st.async pushes that
+                          // complete a transaction count on the RECEIVER's mbarrier; no barrier.cluster inside the loop
+#endif
 #ifndef FUSED_SCALAR_FMA
 #define FUSED_SCALAR_FMA 0   // 1: fp32 mat-vec with scalar FFMA (A/B against the packed FFMA2 form)
 #endif
@@ -54,7 +62,7 @@ namespace gbdpcg {
 // shared-memory plan (host sizes it, device carves it)
 // ---------------------------------------------------------------------------------------------
 struct FusedPlan {
-    uint32_t mbar_off, red_off, cred_off, winA_off, winB_off, stage_off, psm_off, total;
+    uint32_t mbar_off, red_off, cred_off, winA_off, winB_off, stage_off, psm_off, ghost_off, xbar_off, total;
 };
 // nstage: number of matrices the staging area holds side by side (2: S and Phi^-1 for P_REG; else 1)
 // PMODE == P_SMEM keeps Phi^-1 resident in its own area (psm) for the whole solve.
@@ -71,6 +79,9 @@ __host__ __device__ inline FusedPlan make_fused_plan(int nx, int nxp, int bpc, i
     const uint32_t mat = (uint32_t)round_up(bpc * 3 * nx * nx * (int)sizeof(T), 16);
     p.psm_off = o;   o += (pmode == P_SMEM) ? mat : 0;
     p.stage_off = o; o += (uint32_t)nstage * mat;
+    // cluster-mode extras go last, so that the single-CTA layout (the batched hot path) is what it was measured with
+    p.ghost_off = o; o += (uint32_t)round_up(8 * nxp * (int)sizeof(T), 16);   // ghost r [2 sides], s [2], w [2 parities][2 sides]
+    p.xbar_off = o;  o += 32;                                                 // push mode: halo[2] and reduction[2] mbarriers
     p.total = o;
     return p;
 }
@@ -108,6 +119,47 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+
+// ---- one-sided pushes between the CTAs of a cluster: the store lands in the receiver's shared memory and completes
+// `bytes` of the transaction count of the receiver's mbarrier, which the receiver alone waits on ----
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local_addr, uint32_t cta_rank)
+{
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(cta_rank));
+    return r;
+}
+__device__ __forceinline__ void st_async(uint32_t raddr, float a, uint32_t rmbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f32 [%0], %1, [%2];" ::"r"(raddr), "f"(a), "r"(rmbar) : "memory");
+}
+__device__ __forceinline__ void st_async(uint32_t raddr, double a, uint32_t rmbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.f64 [%0], %1, [%2];" ::"r"(raddr), "d"(a), "r"(rmbar) : "memory");
+}
+__device__ __forceinline__ void st_async2(uint32_t raddr, float a, float b, uint32_t rmbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f32 [%0], {%1, %2}, [%3];" ::"r"(raddr), "f"(a), "f"(b),
+                 "r"(rmbar)
+                 : "memory");
+}
+__device__ __forceinline__ void st_async2(uint32_t raddr, double a, double b, uint32_t rmbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.f64 [%0], {%1, %2}, [%3];" ::"r"(raddr), "d"(a), "d"(b),
+                 "r"(rmbar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait_cluster(uint32_t mbar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAITC_%=:\n"
+        "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONEC_%=;\n"
+        "bra WAITC_%=;\n"
+        "DONEC_%=:\n"
+        "}\n" ::"r"(mbar), "r"(parity) : "memory");
+}
 
 // Cooperative global -> shared copy of `count` contiguous elements (the unpadded image of this CTA's block-rows).
 // Used when the TMA path is not available (source not 16-byte aligned, or Phi^-1 resident in shared memory).
@@ -305,6 +357,17 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
     }
 }
 
+#ifdef GBDPCG_TRACE
+// phase timeline (scripts/ubench/trace_cluster.cu): clock64() of thread 0 of every CTA at the phase boundaries
+__device__ long long g_trace[16][64][8];
+#define FTRACE(m) do { if (t == 0 && it < 64 && blockIdx.x < 16) g_trace[blockIdx.x][it][m] = clock64(); } while (0)
+#else
+#define FTRACE(m) do { } while (0)
+#endif
+
+__device__ __forceinline__ float fma_t(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double fma_t(double a, double b, double c) { return __fma_rn(a, b, c); }
+
 // ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
@@ -327,9 +390,11 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
     T *cred = reinterpret_cast<T *>(smem_raw + plan.cred_off);
     T *winA = reinterpret_cast<T *>(smem_raw + plan.winA_off);
     T *winB = reinterpret_cast<T *>(smem_raw + plan.winB_off);
+    T *ghost_r = reinterpret_cast<T *>(smem_raw + plan.ghost_off), *ghost_s = ghost_r + 2 * NXP, *ghost_w = ghost_r + 4 * NXP;
     T *stage = reinterpret_cast<T *>(smem_raw + plan.stage_off);
     T *psm = reinterpret_cast<T *>(smem_raw + plan.psm_off);
-    const uint32_t mbar = smem_u32(smem_raw + plan.mbar_off);
+    const uint32_t mbar = smem_u32(smem_raw + plan.mbar_off), xbar = smem_u32(smem_raw + plan.xbar_off);
+    (void)xbar;
     const uint32_t mat_bytes_pad = (uint32_t)round_up(bpc * BSZ * (int)sizeof(T), 16);
     T *stageS = stage;
     T *stageP = (PMODE == P_SMEM) ? psm : reinterpret_cast<T *>(reinterpret_cast<unsigned char *>(stage) + mat_bytes_pad);
@@ -362,14 +427,24 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
     for (int i = t; i < 128; i += blockDim.x) red[i] = (T)0;
     for (int i = t; i < 64; i += blockDim.x) cred[i] = (T)0;
     if (t == 0 && use_tma) { mbar_init(mbar, 1); fence_mbar_init(); }
+    // push mode: halo barriers [parity] at xbar, +8, reduction barriers [parity] at xbar+16, +24; one arrival (the owner's
+    // expect_tx) per phase.  Phase bits live in registers and run on across the systems of a batch.
+    uint32_t hb_phase = 0, rb_phase = 0;                   // bit `parity` = phase to wait for next
+    if constexpr (CLUSTERED && FUSED && (FUSED_GHOST != 0) && (FUSED_PUSH != 0)) {
+        if (t == 0) {
+#pragma unroll
+            for (int i = 0; i < 4; i++) mbar_init(xbar + 8 * i, 1);
+            fence_mbar_init();
+        }
+    }
 
     // window B sits at the same offset from window A in every CTA, so one pair of remote pointers serves both
     const int wdelta = (int)((plan.winB_off - plan.winA_off) / sizeof(T));
-    T *winA_prev = nullptr, *winA_next = nullptr;
+    T *winA_prev = nullptr, *winA_next = nullptr, *ghost_w_prev = nullptr, *ghost_w_next = nullptr;
     if constexpr (CLUSTERED) {
         cg::cluster_group cl = cg::this_cluster();
-        if (rank > 0) winA_prev = cl.map_shared_rank(winA, rank - 1);
-        if (rank + 1 < csize) winA_next = cl.map_shared_rank(winA, rank + 1);
+        if (rank > 0) { winA_prev = cl.map_shared_rank(winA, rank - 1); ghost_w_prev = cl.map_shared_rank(ghost_w, rank - 1); }
+        if (rank + 1 < csize) { winA_next = cl.map_shared_rank(winA, rank + 1); ghost_w_next = cl.map_shared_rank(ghost_w, rank + 1); }
     }
     sync_all();
 
@@ -386,16 +461,19 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             for (int i = 0; i < R; i++) dst[i] = x[i];
         }
     };
-    auto publish = [&](const bool toB, const T (&x)[R]) {
+    auto publish = [&](const bool toB, const T (&x)[R], const bool remote = true) {
         const int wo = toB ? wdelta : 0;
         if (active) {
             put(winA + wo + slot, x);
             if constexpr (CLUSTERED) {
-                if (send_prev) put(winA_prev + wo + (bpc + 1) * NXP + r0, x);   // right halo of the previous CTA (always full)
-                if (send_next) put(winA_next + wo + r0, x);                     // left halo of the next CTA
+                if (remote && send_prev) put(winA_prev + wo + (bpc + 1) * NXP + r0, x);   // right halo of the previous CTA (always full)
+                if (remote && send_next) put(winA_next + wo + r0, x);                     // left halo of the next CTA
             }
         }
     };
+    // ghost copies (FUSED_GHOST): which halo sides of this CTA have a neighbour behind them
+    const bool has_left = CLUSTERED && rank > 0 && nb > 0, has_right = CLUSTERED && rank < last_rank;
+    (void)has_left; (void)has_right;
 
     // all-thread reduction of a (value0, value1) pair: bit-identical result in every thread of every CTA.
     // Consecutive reductions alternate between two slots, so a fast warp's next partial can never
@@ -571,23 +649,125 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
 #pragma unroll
             for (int i = 0; i < R; i++) { p[i] = (T)0; s[i] = (T)0; }
             T rcp_gamma = (T)0, rcp_alpha = (T)0;
+            // Cluster mode keeps GHOST copies of the neighbours' boundary block-rows of r (and of s): the neighbour sends its
+            // boundary rows of w with the reduction's barrier, and r_g -= alpha s_g, s_g = w_g + beta s_g are repeated here
+            // with the same alpha, beta and the same fused multiply-adds as on the owner, so the copies are bit-identical to
+            // what an exchange would deliver -- and the publish of r needs only a block barrier.
+            constexpr bool GHOST = CLUSTERED && (FUSED_GHOST != 0);
+            // PUSH: what still crosses CTAs (halo rows of r~, boundary rows of w, reduction partials) is pushed with st.async
+            // into the receiver's shared memory and counted on the receiver's mbarrier, so an exchange costs one DSMEM hop
+            // instead of a release / barrier.cluster / acquire round trip.  Two barriers per purpose, alternating with the
+            // iteration: a CTA can run at most one exchange ahead of its slowest partner (it needs that partner's partial
+            // of the previous reduction), so a message can never land in a phase that is still being filled.
+            constexpr bool PUSH = GHOST && (FUSED_PUSH != 0);
+            constexpr bool R_IN_B = (PMODE == P_NONE);                 // the window that carries r
+            constexpr int GE = (2 * NX + 31) / 32;                     // ghost elements per thread (blockDim.x >= 32)
+            T *const rwin = R_IN_B ? winB : winA;
+            T gr[GE], gs[GE];                                          // ghost r, s of the neighbours' boundary block-rows
+            (void)gr; (void)gs;
+            const uint32_t halo_bytes = (uint32_t)((has_left ? 1 : 0) + (has_right ? 1 : 0)) * NX * (uint32_t)sizeof(T);
+            (void)halo_bytes;
+            if constexpr (GHOST) {
+                publish(R_IN_B, res);
+                sync_all();
+#pragma unroll
+                for (int k = 0; k < GE; k++) {
+                    const int e = t + k * (int)blockDim.x, sd = e / NX, c = e - sd * NX;
+                    gr[k] = (e < 2 * NX) ? rwin[(sd ? bpc + 1 : 0) * NXP + c] : (T)0;
+                    gs[k] = (T)0;
+                }
+            }
+            auto push_rows = [&](T *local_dst, const uint32_t dst_rank, const uint32_t mb_local, const T (&x)[R]) {
+                const uint32_t ra = mapa_u32(smem_u32(local_dst), dst_rank), rm = mapa_u32(mb_local, dst_rank);
+                if constexpr (R == 2) st_async2(ra, x[0], x[1], rm);
+                else {
+#pragma unroll
+                    for (int i = 0; i < R; i++) st_async(ra + (uint32_t)(i * sizeof(T)), x[i], rm);
+                }
+            };
             for (;;) {
+                FTRACE(0);
+                const uint32_t par = it & 1u;
                 if constexpr (PMODE != P_NONE) {
-                    publish(false, res);
-                    sync_all();
+                    publish(false, res, !GHOST);
+                    if constexpr (GHOST) __syncthreads();
+                    else sync_all();
+                    FTRACE(1);
                     mv_P(winA, rt);                        // r~ = Phi^-1 r
+                    FTRACE(2);
+                    if constexpr (PUSH) {
+                        const uint32_t hb = xbar + 8 * par;
+                        if (t == 0) mbar_expect_tx(hb, halo_bytes);
+                        publish(true, rt, false);
+                        if (send_prev) push_rows(winB + (bpc + 1) * NXP + r0, (uint32_t)(rank - 1), hb, rt);
+                        if (send_next) push_rows(winB + r0, (uint32_t)(rank + 1), hb, rt);
+                        __syncthreads();
+                        mbar_wait_cluster(hb, (hb_phase >> par) & 1u);
+                        hb_phase ^= 1u << par;
+                    } else {
+                        publish(true, rt);
+                        sync_all();
+                    }
                 } else {
 #pragma unroll
                     for (int i = 0; i < R; i++) rt[i] = res[i];
+                    publish(true, rt, !GHOST);
+                    if constexpr (GHOST) __syncthreads();
+                    else sync_all();
                 }
-                publish(true, rt);
-                sync_all();
+                FTRACE(3);
                 mv_S(winB, w);                             // w = S r~
+                FTRACE(4);
+                const uint32_t rb = xbar + 16 + 8 * par;
+                (void)rb;
+                if constexpr (PUSH) {
+                    if (t == 0) mbar_expect_tx(rb, (uint32_t)csize * 2u * (uint32_t)sizeof(T) + halo_bytes);
+                    if (send_prev) push_rows(ghost_w + (2 * par + 1) * NXP + r0, (uint32_t)(rank - 1), rb, w);
+                    if (send_next) push_rows(ghost_w + 2 * par * NXP + r0, (uint32_t)(rank + 1), rb, w);
+                } else if constexpr (GHOST) {
+                    // boundary rows of w travel with the reduction's cluster barrier (slots alternate with the iteration)
+                    if (send_prev) put(ghost_w_prev + (2 * par + 1) * NXP + r0, w);
+                    if (send_next) put(ghost_w_next + 2 * par * NXP + r0, w);
+                }
                 T g = (T)0, d = (T)0;
 #pragma unroll
                 for (int i = 0; i < R; i++) { g += res[i] * rt[i]; d += w[i] * rt[i]; }
-                const Pair<T> gd = all_sum(g, d);          // gamma = r.r~ , delta = w.r~
+                Pair<T> gd;
+                if constexpr (PUSH) {
+                    // same arithmetic as all_sum(); the CTA partials are pushed to every CTA (itself included) instead of
+                    // stored and fenced by a cluster barrier
+                    Pair<T> pp(g, d);
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) pp = pp + shfl_xor_pair<T>(pp, o);
+                    T *rd = red + red_slot * 64;
+                    if (lane == 0) {
+                        if constexpr (sizeof(T) == 4) *reinterpret_cast<float2 *>(rd + 2 * warp) = make_float2(pp.x(), pp.y());
+                        else *reinterpret_cast<double2 *>(rd + 2 * warp) = make_double2(pp.x(), pp.y());
+                    }
+                    __syncthreads();
+                    const Pair<T> cs = pair_tree_sum<T, NWP>(rd);
+                    T *cr = cred + red_slot * 32;
+                    if (t < csize)
+                        st_async2(mapa_u32(smem_u32(cr + 2 * rank), (uint32_t)t), cs.x(), cs.y(), mapa_u32(rb, (uint32_t)t));
+                    mbar_wait_cluster(rb, (rb_phase >> par) & 1u);
+                    rb_phase ^= 1u << par;
+                    gd = pair_tree_sum<T, 16>(cr);
+                    red_slot ^= 1;
+                } else {
+                    gd = all_sum(g, d);                    // gamma = r.r~ , delta = w.r~
+                }
+                FTRACE(5);
                 const T gamma = gd.x(), delta = gd.y();
+                // ghost rows of w: loaded now, needed only after alpha is known
+                T gw[GE];
+                (void)gw;
+                if constexpr (GHOST) {
+#pragma unroll
+                    for (int k = 0; k < GE; k++) {
+                        const int e = t + k * (int)blockDim.x, sd = e / NX, c = e - sd * NX;
+                        gw[k] = (e < 2 * NX) ? ghost_w[(2 * par + sd) * NXP + c] : (T)0;
+                    }
+                }
                 if (it > 0 && abs_t(gamma) < a.tol) { hit_max = false; break; }   // reference exit test (pcg.cuh:195)
                 if (it == a.max_iter) break;
                 T beta, alpha;
@@ -599,12 +779,29 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
 #pragma unroll
                 for (int i = 0; i < R; i++) {
                     p[i] = rt[i] + beta * p[i];
-                    s[i] = w[i] + beta * s[i];
                     lam[i] += alpha * p[i];
-                    res[i] -= alpha * s[i];
+                    if constexpr (GHOST) {                 // the very operations the ghost copies repeat below
+                        s[i] = fma_t(beta, s[i], w[i]);
+                        res[i] = fma_t(-alpha, s[i], res[i]);
+                    } else {
+                        s[i] = w[i] + beta * s[i];
+                        res[i] -= alpha * s[i];
+                    }
+                }
+                if constexpr (GHOST) {
+#pragma unroll
+                    for (int k = 0; k < GE; k++) {
+                        const int e = t + k * (int)blockDim.x, sd = e / NX, c = e - sd * NX;
+                        if (e < 2 * NX && (sd ? has_right : has_left)) {
+                            gs[k] = fma_t(beta, gs[k], gw[k]);
+                            gr[k] = fma_t(-alpha, gs[k], gr[k]);
+                            rwin[(sd ? bpc + 1 : 0) * NXP + c] = gr[k];
+                        }
+                    }
                 }
                 rcp_gamma = (T)1 / gamma;
                 rcp_alpha = (T)1 / alpha;
+                FTRACE(6);
                 ++it;
             }
         } else {

@@ -31,9 +31,6 @@ __host__ __device__ constexpr int slab_threads(int nx, int bpc)
     return (bpc + slab_blocks_per_warp(nx) - 1) / slab_blocks_per_warp(nx) * 32;
 }
 
-__device__ __forceinline__ float fma_t(float a, float b, float c) { return fmaf(a, b, c); }
-__device__ __forceinline__ double fma_t(double a, double b, double c) { return fma(a, b, c); }
-
 template <typename T, int NX, int PMODE, bool FUSED, bool CLUSTERED, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) pcg_slab_kernel(const KernelArgs<T> a)
 {
