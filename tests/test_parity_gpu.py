@@ -343,6 +343,38 @@ def test_batched_odd_and_large_state_sizes(nx, N, dt, batch):
         check_against_oracle(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, lam1, it1, ex1, noise_floor=True)
 
 
+@pytest.mark.parametrize("dt,cluster", [(np.float32, 16), (np.float32, 8), (np.float64, 16)])
+def test_batched_ragged_cluster_stays_in_step(dt, cluster):
+    """A persistent ragged cluster over a batch (N = 100 on 16 CTAs: 14 full, one short, one EMPTY; on 8: the last one short):
+    the push-mode exchanges carry their phase bits from one system to the next, systems of different iteration counts
+    alternate, and every result equals the single solve."""
+    torch = _torch()
+    nx, nu, N, batch, nseed = 12, 4, 100, 130, 4
+    tol, max_iter = (1e-6 if dt == np.float32 else 1e-10), 3000
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", dt)
+    Pj = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "jacobi", dt)[1]
+    P[1::2] = Pj[1::2]                                        # odd seeds: block-Jacobi -> about twice the iterations
+    reps = (batch + nseed - 1) // nseed
+    d = lambda a: torch.from_numpy(np.tile(a, (reps, 1))[:batch].copy()).cuda()
+    d_S, d_P, d_g = d(S), d(P), d(gam)
+    d_l = torch.zeros(batch, N * nx, dtype=d_S.dtype, device="cuda")
+    d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+    d_ex = torch.ones(batch, dtype=torch.uint8, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0, cluster=cluster)
+    assert g.plan_query(nx, N, dt, True, cfg)["cluster"] == cluster
+    g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
+    torch.cuda.synchronize()
+    lam, its, exs = d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
+    assert not exs.any()
+    for s in range(nseed):
+        lam1, it1, ex1 = gpu_solve(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, cluster=cluster)
+        idx = np.arange(s, batch, nseed)
+        assert (its[idx] == it1).all()
+        assert all(np.array_equal(lam[i], lam1) for i in idx), "batched result differs from the single solve"
+        check_against_oracle(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, lam1, it1, ex1, noise_floor=True)
+    assert its[0] != its[1]
+
+
 def test_batched_host_entry_point():
     nx, nu, N, dt, tol, max_iter = 14, 7, 32, np.float32, 1e-6, 1000
     batch = 700
