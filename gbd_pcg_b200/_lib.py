@@ -45,6 +45,7 @@ SIGNATURES = {
     "gbdpcg_workspace_create": (C.c_int, [C.POINTER(_VP)]),
     "gbdpcg_workspace_destroy": (None, [_VP]),
     "gbdpcg_plan_query": (C.c_int, [_U32, _U32, C.c_int, C.c_int, _CFG, C.POINTER(PlanInfo)]),
+    "gbdpcg_plan_query_batched": (C.c_int, [_U32, _U32, C.c_int, C.c_int, _U32, _CFG, C.POINTER(PlanInfo)]),
     "gbdpcg_host_alloc": (_VP, [C.c_size_t]),
     "gbdpcg_host_free": (None, [_VP]),
     "gbdpcg_version": (C.c_int, []),

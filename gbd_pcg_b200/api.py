@@ -324,13 +324,14 @@ def schur_recover_dev(state_size, control_size, knot_points, batch, d_Qinv, d_Ri
                  _stream_ptr(stream)))
 
 
-def plan_query(state_size, knot_points, dtype=np.float32, has_pinv=True, config=None) -> dict:
+def plan_query(state_size, knot_points, dtype=np.float32, has_pinv=True, config=None, batch=1) -> dict:
     """What the library would launch for this shape (replaces pcgSharedMemSize / checkPcgOccupancy,
-    reference include/pcg.cuh:13-49)."""
+    reference include/pcg.cuh:13-49).  batch: systems per launch -- a system that needs a thread-block cluster gets a
+    larger one while the whole batch is resident in one wave anyway."""
     info = PlanInfo()
     cfg = (config or pcg_config()).to_c()
-    _lib.check(_lib.lib().gbdpcg_plan_query(int(state_size), int(knot_points), int(np.dtype(dtype) == np.float64),
-                                            int(bool(has_pinv)), C.byref(cfg), C.byref(info)))
+    _lib.check(_lib.lib().gbdpcg_plan_query_batched(int(state_size), int(knot_points), int(np.dtype(dtype) == np.float64),
+                                                    int(bool(has_pinv)), int(batch), C.byref(cfg), C.byref(info)))
     return {k: (getattr(info, k).decode() if k == "kernel" else getattr(info, k)) for k, _ in PlanInfo._fields_}
 
 

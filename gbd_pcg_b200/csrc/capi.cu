@@ -103,9 +103,21 @@ static void fused_variants(bool f64, int nx, int fused, const FusedVariant **tab
     }
 }
 
-// Second-generation kernel: smallest cluster that fits, Phi^-1 in registers when possible.
+// SMs of the current device (148 when there is none to ask: planning also works on a machine without a GPU)
+static int device_sms()
+{
+    int dev = 0, sms = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) {
+        cudaGetLastError();
+        return 148;
+    }
+    return sms;
+}
+
+// Second-generation kernel: Phi^-1 in registers when possible; the smallest cluster that fits -- or, when the whole batch
+// stays resident in one wave anyway, a larger one (latency mode, below).
 template <typename T>
-static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, uint32_t batch, Plan *out)
 {
     constexpr bool f64 = sizeof(T) == 8;
     int fused = 1;                                             // single-reduction recurrence unless asked otherwise (parity measured per dtype)
@@ -139,6 +151,24 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
                 out->generic = false; out->fused_kernel = true; out->v = nullptr; out->cluster = cl; out->bpc = bpc;
                 out->threads = threads; out->nbuf = (v->pmode == P_REG) ? 2 : 1; out->pmode = v->pmode; out->smem = smem;
                 out->fn = v->fn; out->name = v->name; out->rpt = v->rpt; out->fused = v->fused;
+                // Latency mode.  A system that needs a cluster anyway solves faster on a LARGER one -- fewer rows per CTA,
+                // and with the push-mode exchanges a CTA more costs nothing (C3: 63.5 us on 4 CTAs, 55.3 on 16; nx=24,N=64:
+                // 88 -> 55; profiles/clusters_r1e.txt) -- as long as every system of the batch still gets its own cluster in
+                // one wave and a CTA keeps at least two warps.  One CTA with Phi^-1 in registers stays one CTA (C2: 26.7 us
+                // against 37), and large batches keep the smallest cluster: fewest SMs per system.
+                if (cl > 1 && !cfg.cluster && !v->slab && v->fused) {
+                    const unsigned long long sms = (unsigned long long)device_sms();
+                    for (int big = 16; big > cl; big >>= 1) {
+                        if ((unsigned long long)batch * big > sms) continue;
+                        const int bpc2 = ((int)N + big - 1) / big;
+                        const int threads2 = round_up(bpc2 * ((int)nx / v->rpt), 32);
+                        if (threads2 < 64 || threads2 > v->maxt) continue;
+                        const size_t smem2 = make_fused_plan<T>((int)nx, v->nxp, bpc2, v->pmode, v->pmode == P_REG ? 2 : 1).total;
+                        if (smem2 > kMaxDynSmem) continue;
+                        out->cluster = big; out->bpc = bpc2; out->threads = threads2; out->smem = smem2;
+                        break;
+                    }
+                }
                 return true;
             }
         }
@@ -153,13 +183,13 @@ static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
 }
 
 template <typename T>
-static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, uint32_t batch, Plan *out)
 {
     constexpr bool f64 = sizeof(T) == 8;
     const RowsVariant *tab;
     int cnt;
     all_variants(f64, (int)nx, &tab, &cnt);
-    if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK;
+    if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
     if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
         static const int cl_opts[] = {1, 2, 4, 8, 16};
         for (int cl : cl_opts) {
@@ -462,7 +492,7 @@ static int solve_batched_dev(const T *S, const T *Pinv, const T *gamma, T *lambd
     if (rc) return rc;
     const bool has_p = use_pinv(Pinv, cfg);
     Plan p;
-    rc = make_plan<T>(nx, N, has_p, *cfg, &p);
+    rc = make_plan<T>(nx, N, has_p, *cfg, batch, &p);
     if (rc) return rc;
     return launch<T>(p, S, has_p ? Pinv : nullptr, gamma, lambda, nx, N, batch, *cfg, d_iters, d_exits, (cudaStream_t)stream);
 }
@@ -542,7 +572,7 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     if ((rc = ws_reserve_flags(w, batch))) return rc;
 
     Plan p;
-    rc = make_plan<T>(nx, N, has_p, *cfg, &p);
+    rc = make_plan<T>(nx, N, has_p, *cfg, batch, &p);
     if (rc) return rc;
     if ((rc = prepare_fn(p.fn, p.cluster > 1))) return rc;
     int resident = 1;
@@ -765,10 +795,10 @@ static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const
 }
 
 template <typename T>
-static int plan_query(uint32_t nx, uint32_t N, int has_pinv, const gbdpcg_config *cfg, gbdpcg_plan_info *out)
+static int plan_query(uint32_t nx, uint32_t N, int has_pinv, uint32_t batch, const gbdpcg_config *cfg, gbdpcg_plan_info *out)
 {
     Plan p;
-    int rc = make_plan<T>(nx, N, has_pinv != 0, *cfg, &p);
+    int rc = make_plan<T>(nx, N, has_pinv != 0, *cfg, batch ? batch : 1u, &p);
     if (rc) return rc;
     memset(out, 0, sizeof *out);
     out->specialised = p.generic ? 0 : 1;
@@ -876,7 +906,18 @@ int gbdpcg_plan_query(uint32_t nx, uint32_t N, int is_f64, int has_pinv, const g
     if (!cfg) cfg = &def;
     if (!out) return fail(GBDPCG_ERR_INVALID, "out must not be NULL");
     if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
-    return is_f64 ? plan_query<double>(nx, N, has_pinv, cfg, out) : plan_query<float>(nx, N, has_pinv, cfg, out);
+    return is_f64 ? plan_query<double>(nx, N, has_pinv, 1u, cfg, out) : plan_query<float>(nx, N, has_pinv, 1u, cfg, out);
+}
+
+int gbdpcg_plan_query_batched(uint32_t nx, uint32_t N, int is_f64, int has_pinv, uint32_t batch, const gbdpcg_config *cfg,
+                              gbdpcg_plan_info *out)
+{
+    gbdpcg_config def;
+    gbdpcg_config_default(&def);
+    if (!cfg) cfg = &def;
+    if (!out) return fail(GBDPCG_ERR_INVALID, "out must not be NULL");
+    if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
+    return is_f64 ? plan_query<double>(nx, N, has_pinv, batch, cfg, out) : plan_query<float>(nx, N, has_pinv, batch, cfg, out);
 }
 
 void *gbdpcg_host_alloc(size_t bytes)

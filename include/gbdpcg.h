@@ -219,6 +219,11 @@ typedef struct gbdpcg_plan_info {
 } gbdpcg_plan_info;
 GBDPCG_API int gbdpcg_plan_query(uint32_t nx, uint32_t N, int is_f64, int has_pinv, const gbdpcg_config *cfg,
                       gbdpcg_plan_info *out);
+/* The same for a batch of `batch` systems.  gbdpcg_plan_query answers for ONE system (what replaces the reference's
+ * pcgSharedMemSize / checkPcgOccupancy, include/pcg.cuh:13-49); a system that needs a thread-block cluster gets a
+ * larger one when the whole batch is resident in one wave anyway (latency), the smallest that fits otherwise. */
+GBDPCG_API int gbdpcg_plan_query_batched(uint32_t nx, uint32_t N, int is_f64, int has_pinv, uint32_t batch,
+                              const gbdpcg_config *cfg, gbdpcg_plan_info *out);
 
 /* -- pinned host memory for callers that want full-rate copies through the _host entry points. */
 GBDPCG_API void *gbdpcg_host_alloc(size_t bytes);

@@ -59,7 +59,7 @@ def test_config_defaults_match_the_reference():
 
 @pytest.mark.parametrize("nx,N,dtype,cluster,spec", [
     (14, 32, np.float32, 1, 1), (2, 3, np.float32, 1, 1), (14, 64, np.float64, None, 1), (12, 512, np.float32, None, 1),
-    (7, 30, np.float32, 1, 1), (3, 3, np.float64, 1, 1), (20, 32, np.float32, 2, 1), (24, 64, np.float64, None, 1),
+    (7, 30, np.float32, 1, 1), (3, 3, np.float64, 1, 1), (20, 32, np.float32, None, 1), (24, 64, np.float64, None, 1),
     (33, 30, np.float32, 1, 0), (32, 32, np.float64, 1, 0)])
 def test_plan_query_without_gpu(nx, N, dtype, cluster, spec):
     info = g.plan_query(nx, N, dtype, True)

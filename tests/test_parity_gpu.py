@@ -302,8 +302,10 @@ def test_batched_equals_single_and_oracle(shape, batch):
     torch.cuda.synchronize()
     lam, its, exs = d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
     assert not exs.any()
+    # a lone system may be planned on a larger cluster than a batch (latency mode): same cluster for a bit-exact comparison
+    cl = g.plan_query(nx, N, dt, True, cfg, batch=batch)["cluster"]
     for s in range(nseed):
-        lam1, it1, _ = gpu_solve(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter)
+        lam1, it1, _ = gpu_solve(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, cluster=cl)
         idx = np.arange(s, batch, nseed)
         assert (its[idx] == it1).all()
         assert all(np.array_equal(lam[i], lam1) for i in idx), "batched result differs from the single solve"
@@ -330,13 +332,14 @@ def test_batched_odd_and_large_state_sizes(nx, N, dt, batch):
     d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
     d_ex = torch.ones(batch, dtype=torch.uint8, device="cuda")
     cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0)
-    assert g.plan_query(nx, N, dt, True, cfg)["specialised"] == 1
+    plan = g.plan_query(nx, N, dt, True, cfg, batch=batch)
+    assert plan["specialised"] == 1
     g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
     torch.cuda.synchronize()
     lam, its, exs = d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
     assert not exs.any()
     for s in range(nseed):
-        lam1, it1, ex1 = gpu_solve(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter)
+        lam1, it1, ex1 = gpu_solve(S[s], P[s], gam[s], np.zeros(N * nx, dtype=dt), nx, N, tol, max_iter, cluster=plan["cluster"])
         idx = np.arange(s, batch, nseed)
         assert (its[idx] == it1).all()
         assert all(np.array_equal(lam[i], lam1) for i in idx), "batched result differs from the single solve"
