@@ -358,6 +358,23 @@ def run_ours(args):
             g.pcg_solve(hS1, hg1, hl1, NX, N_KNOT, cfg_build)
         lat_hb = time_blocking_calls(host_call_build)
 
+        # ---- the other BASELINE configs (parity cases): single-solve latency, kernel scope, stair preconditioner ----
+        other = {}
+        for name in ("C1", "C3", "C4"):
+            onx, onu, oN, odt, otol, omax = g.synth.CONFIGS[name]
+            if name == "C1":
+                So, Po, go = g.synth.example_system(odt, "stair")
+            else:
+                So, Po, go = g.synth.lqr_schur(onx, onu, oN, 0, "stair", odt)
+            dS, dP, dg = (torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in (So, Po, go))
+            dl = torch.zeros(oN * onx, dtype=dS.dtype, device="cuda")
+            di = torch.zeros(1, dtype=torch.int32, device="cuda")
+            ocfg = g.pcg_config(pcg_exit_tol=otol, pcg_max_iter=omax, empty_pinv=0)
+            lat = time_single_solves(torch, lambda: g.solve_dev_async(onx, oN, dS, dP, dg, dl, ocfg, di, None), dl, n_warm=20, n_timed=200)
+            plan = g.plan_query(onx, oN, odt, True, ocfg)
+            other[name] = {"nx": onx, "knot_points": oN, "dtype": np.dtype(odt).name, "iters": int(di.item()), "kernel_p50_us": pct(lat, 0.5),
+                           "kernel_p99_us": pct(lat, 0.99), "cluster": plan["cluster"], "threads": plan["threads"]}
+
         # ---- CPU baseline: host oracle on a bounded sample, all cores ----
         from oracle import oracle
         cores = os.cpu_count() or 1
@@ -404,6 +421,7 @@ def run_ours(args):
                              "dev_api_p50_us": pct(lat_d, 0.5), "dev_api_p99_us": pct(lat_d, 0.99),
                              "host_api_p50_us": pct(lat_h, 0.5), "host_api_p99_us": pct(lat_h, 0.99),
                              "host_api_device_built_pinv_p50_us": pct(lat_hb, 0.5), "host_api_device_built_pinv_p99_us": pct(lat_hb, 0.99)},
+            "other_configs": other,
             "cpu_baseline": {"value": ns / t_cpu, "unit": "solves/s", "cores": cores, "kind": "port",
                              "sample": f"{ns} of the {batch} systems, host oracle (oracle/pcg_oracle.c), {cores} threads",
                              "single_thread_solve_us": t_cpu1 * 1e6, "iters_mean": float(it_c.mean())},
