@@ -361,8 +361,12 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
 // phase timeline (scripts/ubench/trace_cluster.cu): clock64() of thread 0 of every CTA at the phase boundaries
 __device__ long long g_trace[16][64][8];
 #define FTRACE(m) do { if (t == 0 && it < 64 && blockIdx.x < 16) g_trace[blockIdx.x][it][m] = clock64(); } while (0)
+// fixed costs of a solve: entry, init done, matrices arrived, rows in registers, loop entered, loop left, outputs written
+__device__ long long g_trace_fix[16][8];
+#define XTRACE(m) do { if (threadIdx.x == 0 && blockIdx.x < 16) g_trace_fix[blockIdx.x][m] = clock64(); } while (0)
 #else
 #define FTRACE(m) do { } while (0)
+#define XTRACE(m) do { } while (0)
 #endif
 
 __device__ __forceinline__ float fma_t(float a, float b, float c) { return __fmaf_rn(a, b, c); }
@@ -537,6 +541,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         }
     };
     uint32_t phase = 0;
+    XTRACE(1);
     if (use_tma && t == 0 && nb > 0 && cluster_id < a.batch) issue_prefetch(cluster_id);
 
     for (uint32_t prob = cluster_id; prob < a.batch; prob += n_clusters) {
@@ -594,8 +599,10 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             }
             __syncthreads();
         }
+        XTRACE(2);
         load_rows(Sreg, stageS);
         if constexpr (PMODE == P_REG) load_rows(Preg, stageP);
+        XTRACE(3);
         if constexpr (PMODE == P_SMEM) {
             // Phi^-1 stays in shared memory: clear its padding blocks in place (this CTA's first / last block-row)
             __syncthreads();
@@ -849,6 +856,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             }
         }
 
+        XTRACE(5);
         // ---- outputs                                                            (pcg.cuh:212-215) ----
         if (active) {
 #pragma unroll
@@ -862,6 +870,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         // the last reduction, and the partial-sum slots alternate.
     }
     if constexpr (CLUSTERED) cg::this_cluster().sync();   // no CTA may exit while a neighbour can still store into it
+    XTRACE(6);
 }
 
 }  // namespace gbdpcg

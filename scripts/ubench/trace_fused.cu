@@ -62,19 +62,18 @@ int main(int argc, char **argv)
 #ifndef GBDPCG_TRACE
     return 0;
 #else
-    static long long tr[8][64][16];
+    static long long tr[16][64][8], fx[16][8];
     cudaMemcpyFromSymbol(tr, g_trace, sizeof tr);
-    const char *names[] = {"top", "pub r + BAR", "mv_P", "pub rt + BAR", "mv_S", "dots+shfl", "STS+BAR", "tree", "scalars+upd"};
-    for (int w : {0, TR_N * 7 / 32 - 1}) {
-        printf("warp %d: cycles per phase, iterations 8..11\n", w);
-        for (int it = 8; it < 12 && it < iters; it++) {
-            printf("  it %2d:", it);
-            for (int m = 1; m <= 8; m++) printf(" %s=%lld", names[m], tr[w][it][m] - tr[w][it][m - 1]);
-            printf(" | total %lld (to next top %lld)\n", tr[w][it][8] - tr[w][it][0], tr[w][it + 1][0] - tr[w][it][0]);
-        }
+    cudaMemcpyFromSymbol(fx, g_trace_fix, sizeof fx);
+    const char *names[] = {"top", "pub r+BAR", "mv_P", "pub rt+BAR", "mv_S", "dots+all_sum", "scalars+upd"};
+    for (int it = 8; it < 12 && it < iters; it++) {
+        printf("  it %2d:", it);
+        for (int m = 1; m <= 6; m++) printf(" %s=%lld", names[m], tr[0][it][m] - tr[0][it][m - 1]);
+        printf(" | total %lld (to next top %lld)\n", tr[0][it][6] - tr[0][it][0], tr[0][it + 1][0] - tr[0][it][0]);
     }
-    long long span = tr[0][iters - 1][8] - tr[0][0][0];
-    printf("warp 0: %lld cycles for %d iterations = %.1f cycles/iteration\n", span, iters, (double)span / iters);
+    // fixed costs of the LAST system this CTA solved (thread 0): clocks from kernel entry
+    printf("fixed: init done +%lld, matrices arrived +%lld, rows in registers +%lld, first iteration top +%lld, loop left +%lld, kernel end +%lld\n",
+           fx[0][1] - fx[0][0], fx[0][2] - fx[0][0], fx[0][3] - fx[0][0], tr[0][0][0] - fx[0][0], fx[0][5] - fx[0][0], fx[0][6] - fx[0][0]);
     return 0;
 #endif
 }
