@@ -378,6 +378,32 @@ def test_batched_ragged_cluster_stays_in_step(dt, cluster):
     assert its[0] != its[1]
 
 
+@pytest.mark.parametrize("nx,nu,N,dt,cluster,batch", [(14, 7, 64, np.float64, 0, 1), (12, 4, 100, np.float32, 16, 40), (20, 10, 32, np.float32, 0, 64)])
+def test_clustered_solver_is_deterministic(nx, nu, N, dt, cluster, batch):
+    """Push-mode exchanges: a message that arrived early, late or in the wrong phase would change a reduction or a halo row.
+    300 repeats of the same launch (several clusters in flight when batch > 1) must be bit-identical (scripts/stress_cluster.py
+    is the long form)."""
+    torch = _torch()
+    nseed = min(batch, 4)
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", dt)
+    k = (batch + nseed - 1) // nseed
+    d = lambda a: torch.from_numpy(np.tile(a, (k, 1))[:batch].copy()).cuda()
+    d_S, d_P, d_g = d(S), d(P), d(gam)
+    d_l = torch.zeros(batch, N * nx, dtype=d_S.dtype, device="cuda")
+    d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=1e-6 if dt == np.float32 else 1e-10, pcg_max_iter=3000, empty_pinv=0, cluster=cluster)
+    assert g.plan_query(nx, N, dt, True, cfg, batch=batch)["cluster"] > 1
+    ref = None
+    for r in range(300):
+        d_l.zero_()
+        g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, None)
+        if ref is None:
+            ref = (d_l.clone(), d_it.clone())
+        else:
+            assert torch.equal(d_l, ref[0]) and torch.equal(d_it, ref[1]), f"run {r} differs"
+    assert int(d_it.min().item()) > 5
+
+
 def test_batched_host_entry_point():
     nx, nu, N, dt, tol, max_iter = 14, 7, 32, np.float32, 1e-6, 1000
     batch = 700
