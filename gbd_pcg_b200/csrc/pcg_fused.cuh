@@ -44,6 +44,19 @@
 #ifndef FUSED_QBUF
 #define FUSED_QBUF 2
 #endif
+#ifndef FUSED_NCH_F64
+#define FUSED_NCH_F64 4   // accumulation chains per row of the fp64 mat-vec.  14 chains shorten the mat-vec in the trace harness
+                          // (713 -> 519 clk) but cost spills in the real kernels: C3 55.3 -> 57.4 us, (10,5,20) 36.9 -> 38.9 us
+#endif
+#ifndef FUSED_GENERIC_HOIST
+#define FUSED_GENERIC_HOIST 1   // generic (fp64 / odd-nx) mat-vec: issue a window block's loads together, ahead of its multiply-adds
+#endif
+#ifndef FUSED_WAIT_CLUSTER_SCOPE
+// 1: the receiver waits with try_wait.acquire.cluster (what the memory model asks for data pushed by another CTA).  0: the
+// default CTA-scope form, which spares the CCTL.IVALL ptxas emits after a cluster-scope acquire -- measured: no difference
+// (36.80 vs 36.83 us on the C4 trace), so the formally correct form stays.
+#define FUSED_WAIT_CLUSTER_SCOPE 1
+#endif
 #ifndef FUSED_GHOST
 #define FUSED_GHOST 1     // cluster mode, single-reduction recurrence: neighbours' boundary block-rows of r are kept as ghost
                           // copies (updated locally from w, alpha, beta) instead of being exchanged -> one cluster barrier less
@@ -154,7 +167,11 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t mbar, uint32_t parity
         "{\n"
         ".reg .pred p;\n"
         "WAITC_%=:\n"
+#if FUSED_WAIT_CLUSTER_SCOPE
         "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%0], %1;\n"
+#else
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+#endif
         "@p bra DONEC_%=;\n"
         "bra WAITC_%=;\n"
         "DONEC_%=:\n"
@@ -326,7 +343,8 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
         }
     } else {
         constexpr int V = Geo<T>::V;
-        constexpr int NCH = 4;
+        // independent accumulation chains per row (knob for fp64, see FUSED_NCH_F64)
+        constexpr int NCH = (sizeof(T) == 8) ? FUSED_NCH_F64 : 4;
         T acc[R][NCH];
 #pragma unroll
         for (int row = 0; row < R; row++)
@@ -335,13 +353,19 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
         int idx = 0;
 #pragma unroll
         for (int j = 0; j < 3; j++) {
+            // all 16-byte loads of one window block first, then its multiply-adds: with one or two warps per sub-partition
+            // nothing else hides a load-use stall, and ptxas otherwise sinks every load next to its first use
+            constexpr int NQ = (NX + V - 1) / V;
+            typename Vec16<T>::type qv[NQ];
 #pragma unroll
-            for (int c = 0; c < NX; c += V) {
-                const typename Vec16<T>::type q = *reinterpret_cast<const typename Vec16<T>::type *>(w + j * NXP + c);
-                const int k = j * NX + c;
+            for (int i = 0; i < NQ; i++) qv[i] = *reinterpret_cast<const typename Vec16<T>::type *>(w + j * NXP + i * V);
+            if constexpr (FUSED_GENERIC_HOIST != 0) asm volatile("" ::: "memory");
+#pragma unroll
+            for (int i = 0; i < NQ; i++) {
+                const int c = i * V, k = j * NX + c;
                 T qq[4];
-                if constexpr (V == 4) { qq[0] = q.x; qq[1] = q.y; qq[2] = q.z; qq[3] = q.w; }
-                else { qq[0] = q.x; qq[1] = q.y; qq[2] = (T)0; qq[3] = (T)0; }
+                if constexpr (V == 4) { qq[0] = qv[i].x; qq[1] = qv[i].y; qq[2] = qv[i].z; qq[3] = qv[i].w; }
+                else { qq[0] = qv[i].x; qq[1] = qv[i].y; qq[2] = (T)0; qq[3] = (T)0; }
 #pragma unroll
                 for (int e = 0; e < V; e++) {
                     if (c + e < NX) {
@@ -351,9 +375,17 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
                 }
                 idx += V;
             }
+            if constexpr (FUSED_GENERIC_HOIST != 0) asm volatile("" ::: "memory");
         }
 #pragma unroll
-        for (int row = 0; row < R; row++) y[row] = (acc[row][0] + acc[row][1]) + (acc[row][2] + acc[row][3]);
+        for (int row = 0; row < R; row++) {
+#pragma unroll
+            for (int n = NCH; n > 1; n = (n + 1) / 2) {
+#pragma unroll
+                for (int i = 0; i < n / 2; i++) acc[row][i] = acc[row][i] + acc[row][i + (n + 1) / 2];
+            }
+            y[row] = acc[row][0];
+        }
     }
 }
 
