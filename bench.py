@@ -183,7 +183,7 @@ def run_ours(args):
     d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
     d_ex = torch.zeros(batch, dtype=torch.uint8, device="cuda")
     cfg = g.pcg_config(pcg_exit_tol=TOL, pcg_max_iter=MAX_ITER, empty_pinv=0)
-    plan = g.plan_query(NX, N_KNOT, DTYPE, True, cfg)
+    plan = g.plan_query(NX, N_KNOT, DTYPE, True, cfg, batch=batch)
 
     def step():
         g.solve_batched_dev(NX, N_KNOT, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
@@ -371,9 +371,9 @@ def run_ours(args):
             di = torch.zeros(1, dtype=torch.int32, device="cuda")
             ocfg = g.pcg_config(pcg_exit_tol=otol, pcg_max_iter=omax, empty_pinv=0)
             lat = time_single_solves(torch, lambda: g.solve_dev_async(onx, oN, dS, dP, dg, dl, ocfg, di, None), dl, n_warm=20, n_timed=200)
-            plan = g.plan_query(onx, oN, odt, True, ocfg)
+            oplan = g.plan_query(onx, oN, odt, True, ocfg)
             other[name] = {"nx": onx, "knot_points": oN, "dtype": np.dtype(odt).name, "iters": int(di.item()), "kernel_p50_us": pct(lat, 0.5),
-                           "kernel_p99_us": pct(lat, 0.99), "cluster": plan["cluster"], "threads": plan["threads"]}
+                           "kernel_p99_us": pct(lat, 0.99), "cluster": oplan["cluster"], "threads": oplan["threads"]}
 
         # ---- CPU baseline: host oracle on a bounded sample, all cores ----
         from oracle import oracle
