@@ -16,6 +16,7 @@
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
 #include "pcg_slab.cuh"
+#include "pcg_tmem.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
 #include "pinv_build.h"
@@ -60,6 +61,7 @@ static constexpr size_t kMaxDynSmem = 227 * 1024;  // sm_100: 227 KB opt-in dyna
 struct Plan {
     bool generic = false;
     bool fused_kernel = false;        // second-generation kernel (pcg_fused.cuh)
+    bool tmem_kernel = false;         // tensor-memory batched kernel (pcg_tmem.cuh)
     int rpt = 1, fused = 0;           // rows per thread, single-reduction recurrence
     const RowsVariant *v = nullptr;
     int cluster = 1, bpc = 0, threads = 0, nbuf = 1, pmode = P_NONE;
@@ -182,6 +184,26 @@ static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
     return make_smem_plan<T>(v->nx, v->nxp, v->sb, bpc, nbuf).total;
 }
 
+const void *tmem_kernel_f32(int nx, const char **name);   // pcg_tmem_inst.cu
+
+// Tensor-memory batched kernel (pcg_tmem.cuh): fp32, Phi^-1 given, even nx <= 16, one CTA of <= 256 threads per system,
+// default recurrence.  Two systems per SM; worth it only when the batch fills the GPU twice over.
+static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+{
+    if (!has_p || (nx & 1u) || nx > 16 || N < 2 || cfg.cluster > 1) return false;
+    if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA)) return false;
+    const char *name = nullptr;
+    const void *fn = tmem_kernel_f32((int)nx, &name);
+    if (!fn) return false;
+    const int threads = round_up((int)(N * nx / 2), 32);
+    if (threads > kTmemMaxThreads) return false;
+    const size_t smem = make_tmem_plan((int)nx, Geo<float>::nxp((int)nx), (int)N).total;
+    if (2 * (smem + 1024) > 233472) return false;          // two CTAs per SM or it is pointless
+    out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->v = nullptr; out->cluster = 1; out->bpc = (int)N;
+    out->threads = threads; out->nbuf = 1; out->pmode = P_REG; out->smem = smem; out->fn = fn; out->name = name; out->rpt = 2; out->fused = 1;
+    return true;
+}
+
 template <typename T>
 static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, uint32_t batch, Plan *out)
 {
@@ -189,6 +211,11 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     const RowsVariant *tab;
     int cnt;
     all_variants(f64, (int)nx, &tab, &cnt);
+    if (cfg.flags & GBDPCG_FLAG_TMEM) {
+        if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, out)) return GBDPCG_OK; }
+        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 only (nx=%u N=%u %s)", nx, N,
+                    f64 ? "f64" : "f32");
+    }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
     if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
         static const int cl_opts[] = {1, 2, 4, 8, 16};
@@ -302,6 +329,26 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
     if (resident < 1)
         return fail(GBDPCG_ERR_UNSUPPORTED, "kernel %s cannot become resident (cluster=%d threads=%d smem=%zu)", p.name, p.cluster,
                     p.threads, p.smem);
+    if (p.tmem_kernel) {
+        // 256 of the SM's 512 tensor-memory columns per CTA: never more than two CTAs per SM; bulk copies only
+        {
+            // the occupancy query answers 1 per SM for 2 x 80 KB unless the kernel asks for the full shared-memory carveout
+            static std::mutex mu;
+            static std::vector<std::pair<const void *, int>> done;
+            int dev;
+            CK(cudaGetDevice(&dev));
+            std::lock_guard<std::mutex> lk(mu);
+            bool seen = false;
+            for (auto &d : done) seen = seen || (d.first == p.fn && d.second == dev);
+            if (!seen) {
+                CK(cudaFuncSetAttribute(p.fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+                done.push_back({p.fn, dev});
+            }
+        }
+        resident = 2 * device_sms();                       // plan_tmem checked that two CTAs fit an SM
+        if (((uintptr_t)S % 16) || ((uintptr_t)P % 16) || ((3ull * N * nx * nx * sizeof(T)) % 16))
+            return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM needs 16-byte aligned S and Pinv");
+    }
     const uint32_t n_groups = batch < (uint32_t)resident ? batch : (uint32_t)resident;
 
     KernelArgs<T> a;

@@ -19,7 +19,7 @@ if what in ("batched", "all"):
     d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // nseed, 1) for a in (S, P, gam))
     d_l = torch.zeros(batch, N * nx, dtype=torch.float32, device="cuda")
     d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
-    cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0)
+    cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0, flags=int(os.environ.get("PROF_FLAGS", "0"), 0))
     for _ in range(3):
         d_l.zero_()
         g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, None)
