@@ -216,6 +216,16 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 only (nx=%u N=%u %s)", nx, N,
                     f64 ? "f64" : "f32");
     }
+    // Throughput mode: a batch that fills the GPU twice over, of systems that the register-row kernel can only hold one
+    // per SM (more than 128 threads at 255 registers), goes to the tensor-memory kernel -- two systems per SM, same
+    // arithmetic bit for bit (C5: 1.18 -> 1.02 ms; nx=16,N=30: 1.43 -> 1.00; profiles/tmem_r1g.txt).
+    if constexpr (!f64) {
+        const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
+                                  GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA;
+        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && (unsigned long long)batch >= 2ull * (unsigned long long)device_sms() &&
+            N * nx / 2 > 128 && plan_tmem(nx, N, has_p, cfg, out))
+            return GBDPCG_OK;
+    }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
     if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
         static const int cl_opts[] = {1, 2, 4, 8, 16};
@@ -294,6 +304,10 @@ static int max_resident_problems(const Plan &p, int *out)
             }
     }
     CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    if (p.tmem_kernel) {
+        *out = 2 * sms;                                    // 256 of the SM's 512 tensor-memory columns per CTA; plan_tmem checked shared memory and registers
+        return GBDPCG_OK;
+    }
     if (p.cluster == 1) {
         int per_sm = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p.fn, p.threads, p.smem));
@@ -345,9 +359,15 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
                 done.push_back({p.fn, dev});
             }
         }
-        resident = 2 * device_sms();                       // plan_tmem checked that two CTAs fit an SM
-        if (((uintptr_t)S % 16) || ((uintptr_t)P % 16) || ((3ull * N * nx * nx * sizeof(T)) % 16))
-            return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM needs 16-byte aligned S and Pinv");
+        if (((uintptr_t)S % 16) || ((uintptr_t)P % 16) || ((3ull * N * nx * nx * sizeof(T)) % 16)) {
+            if (cfg.flags & GBDPCG_FLAG_TMEM) return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM needs 16-byte aligned S and Pinv");
+            // chosen by the planner: fall back to the register-row kernel, which can stage with ordinary loads
+            gbdpcg_config c2 = cfg;
+            c2.flags |= GBDPCG_FLAG_NO_TMEM;
+            Plan p2;
+            if ((rc = make_plan<T>(nx, N, P != nullptr, c2, batch, &p2))) return rc;
+            return launch<T>(p2, S, P, gamma, lambda, nx, N, batch, c2, d_iters, d_exits, stream);
+        }
     }
     const uint32_t n_groups = batch < (uint32_t)resident ? batch : (uint32_t)resident;
 

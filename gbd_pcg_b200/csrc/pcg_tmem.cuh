@@ -229,10 +229,11 @@ __global__ void __launch_bounds__(kTmemMaxThreads, 2) pcg_tmem_kernel(const Kern
             if (t == 0 && next < a.batch) { fence_proxy_async(); issue_copy(a.Pinv + (size_t)next * a.mat_stride); }
         }
 
-        auto mv_S = [&](const T *win, T (&y)[R]) {
+        // The first tensor-memory load of a mat-vec does not depend on the window: the caller issues it BEFORE the barrier
+        // that publishes the vector (u0), so its latency hides behind the barrier.
+        auto mv_S = [&](const T *win, uint32_t (&ua)[16], T (&y)[R]) {
             const T *w = win + wofs;
-            uint32_t ua[16], ub[16];
-            tmem_ld16(tS, ua);                             // arrives behind the two register blocks
+            uint32_t ub[16];
             float2 acc[R][NCH];
 #pragma unroll
             for (int row_ = 0; row_ < R; row_++)
@@ -263,10 +264,9 @@ __global__ void __launch_bounds__(kTmemMaxThreads, 2) pcg_tmem_kernel(const Kern
             }
             finish(acc, y);
         };
-        auto mv_P = [&](const T *win, T (&y)[R]) {
+        auto mv_P = [&](const T *win, uint32_t (&u0)[16], T (&y)[R]) {
             const T *w = win + wofs;
-            uint32_t u[2][16];
-            tmem_ld16(tP, u[0]);
+            uint32_t u1[16];
             float2 acc[R][NCH];
 #pragma unroll
             for (int row_ = 0; row_ < R; row_++)
@@ -274,18 +274,26 @@ __global__ void __launch_bounds__(kTmemMaxThreads, 2) pcg_tmem_kernel(const Kern
                 for (int ch = 0; ch < NCH; ch++) acc[row_][ch] = make_float2(0.f, 0.f);
 #pragma unroll
             for (int c = 0; c < NCP; c++) {
-                tmem_wait_ld(u[c & 1]);
-                if (c + 1 < NCP) tmem_ld16(tP + 16 * (c + 1), u[(c + 1) & 1]);
-                fma_chunk(c / CPB, c % CPB, u[c & 1], w, acc);
+                if (c & 1) {
+                    tmem_wait_ld(u1);
+                    if (c + 1 < NCP) tmem_ld16(tP + 16 * (c + 1), u0);
+                    fma_chunk(c / CPB, c % CPB, u1, w, acc);
+                } else {
+                    tmem_wait_ld(u0);
+                    if (c + 1 < NCP) tmem_ld16(tP + 16 * (c + 1), u1);
+                    fma_chunk(c / CPB, c % CPB, u0, w, acc);
+                }
             }
             finish(acc, y);
         };
 
         // ---- r = gamma - S*lambda                                               (pcg.cuh:118-126) ----
         T res[R], rt[R], w[R], p[R], s[R];
+        uint32_t u0[16];
         publish(winB, lam);
+        tmem_ld16(tS, u0);
         __syncthreads();
-        mv_S(winB, w);
+        mv_S(winB, u0, w);
 #pragma unroll
         for (int i = 0; i < R; i++) { res[i] = gam[i] - w[i]; p[i] = 0.f; s[i] = 0.f; }
 
@@ -294,11 +302,13 @@ __global__ void __launch_bounds__(kTmemMaxThreads, 2) pcg_tmem_kernel(const Kern
         T rcp_gamma = 0.f, rcp_alpha = 0.f;
         for (;;) {
             publish(winA, res);
+            tmem_ld16(tP, u0);
             __syncthreads();
-            mv_P(winA, rt);                                // r~ = Phi^-1 r                (pcg.cuh:131-140, 181-184)
+            mv_P(winA, u0, rt);                            // r~ = Phi^-1 r                (pcg.cuh:131-140, 181-184)
             publish(winB, rt);
+            tmem_ld16(tS, u0);
             __syncthreads();
-            mv_S(winB, w);                                 // w = S r~
+            mv_S(winB, u0, w);                             // w = S r~
             T g = 0.f, d = 0.f;
 #pragma unroll
             for (int i = 0; i < R; i++) { g += res[i] * rt[i]; d += w[i] * rt[i]; }

@@ -75,6 +75,7 @@ typedef struct gbdpcg_config {
  * PRECONDITIONED solve, and it halves the bytes a host-resident batch has to push over PCIe. */
 #define GBDPCG_FLAG_TMEM 0x400u         /* fp32 batched: two systems per SM, Phi^-1 and the right blocks of S in tensor memory
                                            (pcg_tmem.cuh); GBDPCG_ERR_UNSUPPORTED for shapes it does not cover */
+#define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick the tensor-memory kernel (the planner takes it for fp32 batches >= 2 x SMs) */
 #define GBDPCG_FLAG_BUILD_JACOBI 0x100u
 #define GBDPCG_FLAG_BUILD_STAIR 0x200u
 

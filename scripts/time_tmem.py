@@ -1,4 +1,4 @@
-"""A/B of the tensor-memory batched kernel (GBDPCG_FLAG_TMEM, two systems per SM) against the default register-row kernel:
+"""A/B of the tensor-memory batched kernel (GBDPCG_FLAG_TMEM, two systems per SM) against the register-row kernel (GBDPCG_FLAG_NO_TMEM):
 lambda and iteration counts must be bit-identical; launch time of both.   usage: python scripts/time_tmem.py [batch]"""
 import os
 import sys
@@ -9,14 +9,14 @@ import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import gbd_pcg_b200 as g  # noqa: E402
 
-FLAG_TMEM = 0x400
+FLAG_TMEM, FLAG_NO_TMEM = 0x400, 0x800
 batch = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 nseed = 64
 for (nx, nu, N) in [(14, 7, 32), (12, 4, 40), (16, 8, 30), (8, 4, 60), (10, 5, 17)]:
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", np.float32)
     d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // nseed, 1) for a in (S, P, gam))
     out = {}
-    for name, flags in (("default", 0), ("tmem", FLAG_TMEM)):
+    for name, flags in (("default", FLAG_NO_TMEM), ("tmem", FLAG_TMEM)):
         d_l = torch.zeros(batch, N * nx, dtype=torch.float32, device="cuda")
         d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
         d_ex = torch.zeros(batch, dtype=torch.uint8, device="cuda")

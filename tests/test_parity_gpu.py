@@ -550,3 +550,101 @@ def test_unaligned_device_pointers_fall_back_from_tma():
     cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter)
     it = g.api._solve_dev(nx, N, d_S, d_P, d_g, d_l, config=cfg)
     assert it == it_a and np.array_equal(d_l.cpu().numpy(), lam_a)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# tensor-memory batched kernel (pcg_tmem.cuh): two systems per SM, Phi^-1 and the right blocks of S in TMEM
+# ---------------------------------------------------------------------------------------------------------------
+def _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags):
+    torch = _torch()
+    d_l = torch.from_numpy(np.ascontiguousarray(lam0)).cuda()
+    d_it = torch.full((batch,), 77, dtype=torch.int32, device="cuda")
+    d_ex = torch.full((batch,), 7, dtype=torch.uint8, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0, flags=flags)
+    g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
+    torch.cuda.synchronize()
+    return d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
+
+
+@pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 32, 700), (14, 7, 32, 5), (12, 4, 40, 301), (16, 8, 30, 297), (8, 4, 60, 330), (10, 5, 17, 1000),
+                                           (14, 7, 2, 64), (16, 8, 32, 40)])
+@pytest.mark.parametrize("precond", ["stair", "jacobi"])
+def test_tmem_kernel_vs_oracle_and_register_kernel(nx, nu, N, batch, precond):
+    """GBDPCG_FLAG_TMEM on ragged batch sizes (fewer systems than CTAs, not a multiple of the grid), the smallest and the
+    largest supported system: every system against the host oracle; against the register-row kernel bit for bit where
+    both reduce over the same number of warp slots."""
+    torch = _torch()
+    nseed = 6
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), precond, np.float32)
+    reps = (batch + nseed - 1) // nseed
+    Sb, Pb, gb = (np.tile(a, (reps, 1))[:batch].copy() for a in (S, P, gam))
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (Sb, Pb, gb))
+    lam0 = np.zeros((batch, N * nx), np.float32)
+    tol, max_iter = 1e-6, 1000
+    assert "pcg_tmem" in g.plan_query(nx, N, np.float32, True, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=batch)["kernel"]
+    lam_t, it_t, ex_t = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, g._lib.FLAG_TMEM)
+    lam_r, it_r, ex_r = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, g._lib.FLAG_NO_TMEM)
+    assert not ex_t.any()
+    assert np.abs(it_t.astype(int) - it_r.astype(int)).max() <= 1
+    if nx in (12, 14, 16) and N * nx // 2 > 128:
+        assert np.array_equal(it_t, it_r) and np.array_equal(lam_t.view(np.uint32), lam_r.view(np.uint32))
+    for s in range(min(nseed, batch)):
+        idx = np.arange(s, batch, nseed)
+        assert (it_t[idx] == it_t[s]).all() and all(np.array_equal(lam_t[i], lam_t[s]) for i in idx)
+        check_against_oracle(S[s], P[s], gam[s], np.zeros(N * nx, np.float32), nx, N, tol, max_iter, lam_t[s], int(it_t[s]), bool(ex_t[s]))
+
+
+def test_tmem_kernel_edge_semantics():
+    """max_iter = 0 leaves lambda, a low cap reports the flag, warm starts, padding blocks never reach the arithmetic."""
+    torch = _torch()
+    nx, nu, N, batch = 14, 7, 32, 300
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(4), "stair", np.float32)
+    Sb, Pb, gb = (np.tile(a, (batch // 4, 1)).copy() for a in (S, P, gam))
+    rng = np.random.default_rng(5)
+    # poison the padding blocks (left of row 0, right of row N-1): the reference never reads them (include/pcg.cuh:105-106)
+    for M in (Sb, Pb):
+        M[:, : nx * nx] = np.nan
+        M[:, (N - 1) * 3 * nx * nx + 2 * nx * nx:] = np.nan
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (Sb, Pb, gb))
+    lam0 = rng.standard_normal((batch, N * nx)).astype(np.float32)
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 0, g._lib.FLAG_TMEM)
+    assert np.array_equal(lam, lam0) and (it == 0).all() and (ex == 1).all()
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 3, g._lib.FLAG_TMEM)
+    assert (it == 3).all() and (ex == 1).all() and np.isfinite(lam).all()
+    lam_w, it_w, ex_w = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, g._lib.FLAG_TMEM)
+    lam_r, it_r, ex_r = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, g._lib.FLAG_NO_TMEM)
+    assert not ex_w.any() and np.array_equal(it_w, it_r) and np.array_equal(lam_w.view(np.uint32), lam_r.view(np.uint32))
+    for s in range(4):
+        check_against_oracle(S[s], P[s], gam[s], lam0[s], nx, N, 1e-6, 1000, lam_w[s], int(it_w[s]), bool(ex_w[s]))
+
+
+def test_tmem_kernel_selection_and_refusals():
+    """The planner takes the tensor-memory kernel for fp32 batches that fill the GPU twice; it is refused (flag forced) or
+    avoided (planner) for fp64, identity preconditioner, odd / large state sizes and unaligned pointers."""
+    torch = _torch()
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0)
+    assert "pcg_tmem" in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms)["kernel"]
+    assert g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms)["max_resident"] == 2 * sms
+    assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms - 1)["kernel"]
+    assert "pcg_tmem" not in g.plan_query(14, 32, np.float64, True, cfg, batch=8192)["kernel"]
+    assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, False, cfg, batch=8192)["kernel"]
+    assert "pcg_tmem" not in g.plan_query(10, 17, np.float32, True, cfg, batch=8192)["kernel"]      # 85 threads: several CTAs per SM anyway
+    assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, g.pcg_config(flags=g._lib.FLAG_NO_TMEM), batch=8192)["kernel"]
+    for (nx, N, dt, has_p) in [(14, 32, np.float64, True), (14, 32, np.float32, False), (15, 20, np.float32, True), (18, 20, np.float32, True),
+                               (14, 40, np.float32, True)]:
+        with pytest.raises(g.GbdpcgError):
+            g.plan_query(nx, N, dt, has_p, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=8192)
+    # unaligned S / Pinv: the planner's choice falls back to the register-row kernel, same results
+    nx, nu, N, batch = 14, 7, 32, 2 * sms
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(4), "stair", np.float32)
+    Sb, Pb, gb = (np.tile(a, (batch // 4, 1)).copy() for a in (S, P, gam))
+    pad = lambda a: torch.from_numpy(np.concatenate([np.zeros(1, a.dtype), a.ravel()])).cuda()[1:]
+    d_S, d_P, d_g = pad(Sb), pad(Pb), torch.from_numpy(gb).cuda()
+    assert d_S.data_ptr() % 16 == 4
+    lam0 = np.zeros((batch, N * nx), np.float32)
+    lam_u, it_u, _ = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, 0)
+    lam_a, it_a, _ = _batched(nx, N, batch, torch.from_numpy(Sb).cuda(), torch.from_numpy(Pb).cuda(), d_g, lam0, 1e-6, 1000, 0)
+    assert np.array_equal(it_u, it_a) and np.array_equal(lam_u, lam_a)
+    with pytest.raises(g.GbdpcgError):
+        _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, g._lib.FLAG_TMEM)
