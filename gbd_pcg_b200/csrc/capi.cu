@@ -198,7 +198,7 @@ static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
     const int threads = round_up((int)(N * nx / 2), 32);
     if (threads > kTmemMaxThreads) return false;
     const size_t smem = make_tmem_plan((int)nx, Geo<float>::nxp((int)nx), (int)N).total;
-    if (2 * (smem + 1024) > 233472) return false;          // two CTAs per SM or it is pointless
+    if ((size_t)(512 / tmem_cols(threads)) * (smem + 1024) > 233472) return false;   // as many CTAs per SM as tensor memory allows, or it is pointless
     out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->v = nullptr; out->cluster = 1; out->bpc = (int)N;
     out->threads = threads; out->nbuf = 1; out->pmode = P_REG; out->smem = smem; out->fn = fn; out->name = name; out->rpt = 2; out->fused = 1;
     return true;
@@ -216,14 +216,16 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 only (nx=%u N=%u %s)", nx, N,
                     f64 ? "f64" : "f32");
     }
-    // Throughput mode: a batch that fills the GPU twice over, of systems that the register-row kernel can only hold one
-    // per SM (more than 128 threads at 255 registers), goes to the tensor-memory kernel -- two systems per SM, same
-    // arithmetic bit for bit (C5: 1.18 -> 1.02 ms; nx=16,N=30: 1.43 -> 1.00; profiles/tmem_r1g.txt).
+    // Throughput mode: a batch that fills every tensor-memory slot of the GPU (two systems per SM above 128 threads per
+    // system, four below) goes to the tensor-memory kernel -- same arithmetic bit for bit (C5: 1.18 -> 1.00 ms; nx=16,N=30:
+    // 1.43 -> 1.00; nx=10,N=17: 0.42 -> 0.35; profiles/tmem_r1g.txt).
     if constexpr (!f64) {
         const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
                                   GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA;
-        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && (unsigned long long)batch >= 2ull * (unsigned long long)device_sms() &&
-            N * nx / 2 > 128 && plan_tmem(nx, N, has_p, cfg, out))
+        // (systems of <= 64 threads lose: the register-row kernel already fits four of them on an SM -- nx=8,N=16: 0.19 vs 0.21 ms)
+        const unsigned long long per_sm = 512ull / (unsigned long long)tmem_cols(round_up((int)(N * nx / 2), 32));
+        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && (unsigned long long)batch >= per_sm * (unsigned long long)device_sms() &&
+            N * nx / 2 > 64 && plan_tmem(nx, N, has_p, cfg, out))
             return GBDPCG_OK;
     }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
@@ -305,7 +307,7 @@ static int max_resident_problems(const Plan &p, int *out)
     }
     CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (p.tmem_kernel) {
-        *out = 2 * sms;                                    // 256 of the SM's 512 tensor-memory columns per CTA; plan_tmem checked shared memory and registers
+        *out = (512 / tmem_cols(p.threads)) * sms;         // 128 or 256 of the SM's 512 tensor-memory columns per CTA; plan_tmem checked shared memory and registers
         return GBDPCG_OK;
     }
     if (p.cluster == 1) {
@@ -344,7 +346,7 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
         return fail(GBDPCG_ERR_UNSUPPORTED, "kernel %s cannot become resident (cluster=%d threads=%d smem=%zu)", p.name, p.cluster,
                     p.threads, p.smem);
     if (p.tmem_kernel) {
-        // 256 of the SM's 512 tensor-memory columns per CTA: never more than two CTAs per SM; bulk copies only
+        // 128 or 256 of the SM's 512 tensor-memory columns per CTA: four or two CTAs per SM; bulk copies only
         {
             // the occupancy query answers 1 per SM for 2 x 80 KB unless the kernel asks for the full shared-memory carveout
             static std::mutex mu;

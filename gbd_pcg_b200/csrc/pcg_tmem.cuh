@@ -69,7 +69,9 @@ __host__ __device__ inline TmemPlan make_tmem_plan(int nx, int nxp, int N)
     p.total = o;
     return p;
 }
-constexpr int kTmemCols = 256;          // per CTA; two CTAs per SM fill the 512 columns
+// TMEM columns per CTA: up to 4 warps each own a lane quarter and 128 columns are enough (four CTAs per SM); 5..8 warps share
+// the quarters two by two and take 256 (two CTAs per SM fill the 512 columns).
+__host__ __device__ constexpr int tmem_cols(int threads) { return threads <= 128 ? 128 : 256; }
 constexpr int kTmemMaxThreads = 256;    // 8 warps: two per TMEM lane quarter
 
 template <int NX>
@@ -104,7 +106,7 @@ __global__ void __launch_bounds__(kTmemMaxThreads, 2) pcg_tmem_kernel(const Kern
     for (int i = t; i < 128; i += blockDim.x) red[i] = 0.f;
     if (t == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(kTmemCols) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(tmem_cols((int)blockDim.x)) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -357,7 +359,7 @@ __global__ void __launch_bounds__(kTmemMaxThreads, 2) pcg_tmem_kernel(const Kern
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(kTmemCols) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(tmem_cols((int)blockDim.x)) : "memory");
 }
 
 }  // namespace gbdpcg

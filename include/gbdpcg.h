@@ -73,9 +73,9 @@ typedef struct gbdpcg_config {
  * the Pinv argument and empty_pinv are then ignored.  This is what makes the reference's own host signature
  * solvePCG<T>(h_S, h_gamma, h_lambda, ...) -- which has no Pinv parameter (include/interface.cuh:24-31) -- a
  * PRECONDITIONED solve, and it halves the bytes a host-resident batch has to push over PCIe. */
-#define GBDPCG_FLAG_TMEM 0x400u         /* fp32 batched: two systems per SM, Phi^-1 and the right blocks of S in tensor memory
+#define GBDPCG_FLAG_TMEM 0x400u         /* fp32 batched: two (or, up to 128 threads per system, four) systems per SM, Phi^-1 and the right blocks of S in tensor memory
                                            (pcg_tmem.cuh); GBDPCG_ERR_UNSUPPORTED for shapes it does not cover */
-#define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick the tensor-memory kernel (the planner takes it for fp32 batches >= 2 x SMs) */
+#define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick the tensor-memory kernel (the planner takes it for fp32 batches that fill its 2 or 4 slots per SM) */
 #define GBDPCG_FLAG_BUILD_JACOBI 0x100u
 #define GBDPCG_FLAG_BUILD_STAIR 0x200u
 

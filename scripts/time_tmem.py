@@ -12,7 +12,10 @@ import gbd_pcg_b200 as g  # noqa: E402
 FLAG_TMEM, FLAG_NO_TMEM = 0x400, 0x800
 batch = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 nseed = 64
-for (nx, nu, N) in [(14, 7, 32), (12, 4, 40), (16, 8, 30), (8, 4, 60), (10, 5, 17)]:
+SHAPES = [(14, 7, 32), (12, 4, 40), (16, 8, 30), (8, 4, 60), (10, 5, 17)]
+if len(sys.argv) > 2 and sys.argv[2] == "small":      # systems of <= 128 threads: 128 TMEM columns per CTA, four CTAs per SM
+    SHAPES = [(10, 5, 17), (8, 4, 30), (12, 6, 20), (14, 7, 16), (16, 8, 16), (8, 4, 16)]
+for (nx, nu, N) in SHAPES:
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", np.float32)
     d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // nseed, 1) for a in (S, P, gam))
     out = {}

@@ -567,7 +567,7 @@ def _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags):
 
 
 @pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 32, 700), (14, 7, 32, 5), (12, 4, 40, 301), (16, 8, 30, 297), (8, 4, 60, 330), (10, 5, 17, 1000),
-                                           (14, 7, 2, 64), (16, 8, 32, 40)])
+                                           (14, 7, 2, 64), (16, 8, 32, 40), (16, 8, 16, 1300), (8, 4, 30, 2000), (12, 6, 20, 777)])
 @pytest.mark.parametrize("precond", ["stair", "jacobi"])
 def test_tmem_kernel_vs_oracle_and_register_kernel(nx, nu, N, batch, precond):
     """GBDPCG_FLAG_TMEM on ragged batch sizes (fewer systems than CTAs, not a multiple of the grid), the smallest and the
@@ -629,7 +629,11 @@ def test_tmem_kernel_selection_and_refusals():
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms - 1)["kernel"]
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float64, True, cfg, batch=8192)["kernel"]
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, False, cfg, batch=8192)["kernel"]
-    assert "pcg_tmem" not in g.plan_query(10, 17, np.float32, True, cfg, batch=8192)["kernel"]      # 85 threads: several CTAs per SM anyway
+    # systems of <= 128 threads take 128 TMEM columns: four CTAs per SM, chosen once the batch fills them
+    assert "pcg_tmem" in g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms)["kernel"]
+    assert g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms)["max_resident"] == 4 * sms
+    assert "pcg_tmem" not in g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms - 1)["kernel"]
+    assert "pcg_tmem" not in g.plan_query(8, 16, np.float32, True, cfg, batch=8192)["kernel"]       # 64 threads: the register-row kernel fits four per SM itself
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, g.pcg_config(flags=g._lib.FLAG_NO_TMEM), batch=8192)["kernel"]
     for (nx, N, dt, has_p) in [(14, 32, np.float64, True), (14, 32, np.float32, False), (15, 20, np.float32, True), (18, 20, np.float32, True),
                                (14, 40, np.float32, True)]:
