@@ -1,4 +1,4 @@
-// pcg_tmem.cuh -- batched fp32 solver with TWO systems resident per SM: Phi^-1 and the right blocks of S live in
+// pcg_tmem.cuh -- batched fp32 solver with TWO (small systems: FOUR) systems resident per SM: Phi^-1 and the right blocks of S live in
 // TENSOR MEMORY (256 KB per SM that the register-row kernel of pcg_fused.cuh leaves idle), the left and diagonal
 // blocks of S in registers.
 //
@@ -18,7 +18,8 @@
 //
 // TMEM layout.  Warp w may touch TMEM lanes 32*(w%4) .. +31 only; lane = the thread's lane, so data is thread-private.
 // Columns (32-bit) per thread: 128 = 8 chunks of 16; warps w and w+4 share a lane quarter and take columns 0..127 and
-// 128..255 of the CTA's 256-column allocation.  Chunk (j, cb) of a matrix holds, for window block j in {left, diag,
+// 128..255 of the CTA's 256-column allocation (a CTA of at most 4 warps allocates 128 columns only, so four such CTAs share an
+// SM).  Chunk (j, cb) of a matrix holds, for window block j in {left, diag,
 // right} and quad pair cb, the entries m(row, j*nx + 8*cb + 4*q + e) at register 8*q + 4*row + e -- exactly the operands
 // of two 16-byte window loads, in the order the FFMA2 chains consume them.  Phi^-1: chunks 0 .. 3*CPB-1, S right block:
 // the following CPB chunks (CPB = chunks per block = ceil(ceil(nx/4)/2) <= 2, i.e. nx <= 16).
