@@ -115,6 +115,45 @@ def _stream_ptr(stream):
     return C.c_void_p(stream.cuda_stream)
 
 
+class workspace:
+    """Per-caller workspace handle (``gbdpcg_workspace_create`` / ``_destroy``, include/gbdpcg.h): cached device buffers,
+    pinned scalars, two streams.  Replaces the 20 allocator calls per solve of the reference host path
+    (include/interface.cuh:39-53,79-86,105-108,140-141).  One workspace per host thread lets callers solve concurrently;
+    ``workspace=None`` in any call selects the process-wide default workspace of the current device (internally locked).
+    Use as a context manager or call ``close()``."""
+
+    def __init__(self):
+        self._h = C.c_void_p(None)
+        _lib.check(_lib.lib().gbdpcg_workspace_create(C.byref(self._h)))
+
+    @property
+    def handle(self):
+        if not self._h:
+            raise ValueError("workspace is closed")
+        return self._h
+
+    def close(self):
+        if self._h:
+            _lib.lib().gbdpcg_workspace_destroy(self._h)
+            self._h = C.c_void_p(None)
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001  (interpreter shutdown)
+            pass
+
+
+def _ws(w):
+    return None if w is None else w.handle
+
+
 # ------------------------------------------------------------------------------------------------
 # reference-shaped entry points
 # ------------------------------------------------------------------------------------------------
@@ -129,12 +168,12 @@ def solvePCG(*args, **kw):
     raise TypeError("solvePCG: unrecognised overload (first argument must be h_S or state_size)")
 
 
-def pcg_solve(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None):
+def pcg_solve(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None, workspace=None):
     """README.md:42 spelling; config defaults like the README's ``default_config``."""
-    return _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config, h_Pinv=h_Pinv)
+    return _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config, h_Pinv=h_Pinv, workspace=workspace)
 
 
-def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None, return_flag=False):
+def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pinv=None, return_flag=False, workspace=None):
     """Host-pointer overload.  ``h_lambda`` is updated in place; returns the iteration count
     (the reference returns 1 unconditionally, include/interface.cuh:88 -- a defect this build does not keep).
     ``h_Pinv`` (extension) supplies Phi^-1; it is used only when ``config.empty_pinv == 0``.  Without it,
@@ -153,7 +192,7 @@ def _solve_host(h_S, h_gamma, h_lambda, stateSize, knotPoints, config=None, h_Pi
             cfg.empty_pinv = 1
     it, ex = C.c_uint32(0), C.c_int32(0)
     f = getattr(_lib.lib(), f"gbdpcg_solve_host_{suf}")
-    _lib.check(f(None, _host(h_S, h_S.dtype, ms, "h_S"),
+    _lib.check(f(_ws(workspace), _host(h_S, h_S.dtype, ms, "h_S"),
                  None if h_Pinv is None else _host(h_Pinv, h_S.dtype, ms, "h_Pinv"),
                  _host(h_gamma, h_S.dtype, vs, "h_gamma"), _host(h_lambda, h_S.dtype, vs, "h_lambda", True),
                  nx, N, C.byref(cfg), C.byref(it), C.byref(ex)))
@@ -204,7 +243,7 @@ def pack_csr_dev(d_row_ptr, d_col_ind, d_val, rows, state_size, knot_points, d_o
 
 
 def _solve_dev(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_r=None, d_p=None, d_v_temp=None,
-               d_eta_new_temp=None, config=None, stream=None, return_flag=False):
+               d_eta_new_temp=None, config=None, stream=None, return_flag=False, workspace=None):
     """Device-pointer overload (blocking, returns iterations like include/interface.cuh:136,143).
     The four scratch buffers of the reference are accepted and ignored.  ``d_Pinv`` is always applied,
     whatever ``config.empty_pinv`` says, because the reference kernel has no notion of that flag
@@ -216,7 +255,7 @@ def _solve_dev(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_r=None
     cfg.empty_pinv = 1 if d_Pinv is None else 0
     it, ex = C.c_uint32(0), C.c_int32(0)
     f = getattr(_lib.lib(), f"gbdpcg_solve_dev_sync_{suf}")
-    _lib.check(f(None, _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv", True), _dev_ptr(d_gamma, "d_gamma"),
+    _lib.check(f(_ws(workspace), _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv", True), _dev_ptr(d_gamma, "d_gamma"),
                  _dev_ptr(d_lambda, "d_lambda"), int(state_size), int(knot_points), C.byref(cfg),
                  C.byref(it), C.byref(ex), _stream_ptr(stream)))
     return (it.value, bool(ex.value)) if return_flag else it.value
@@ -250,7 +289,7 @@ def solve_batched_dev(state_size, knot_points, batch, d_S, d_Pinv, d_gamma, d_la
                  _dev_ptr(d_iters, "d_iters", True), _dev_ptr(d_exit, "d_exit", True), _stream_ptr(stream)))
 
 
-def solve_batched_host(h_S, h_Pinv, h_gamma, h_lambda, state_size, knot_points, batch, config):
+def solve_batched_host(h_S, h_Pinv, h_gamma, h_lambda, state_size, knot_points, batch, config, workspace=None):
     """Blocking batched solve on host arrays (pageable or pinned).  Returns (iters[batch], max_iter_exit[batch])."""
     suf = _suffix(h_S.dtype)
     nx, N, B = int(state_size), int(knot_points), int(batch)
@@ -261,7 +300,7 @@ def solve_batched_host(h_S, h_Pinv, h_gamma, h_lambda, state_size, knot_points, 
     iters = np.zeros(B, dtype=np.uint32)
     exits = np.zeros(B, dtype=np.uint8)
     f = getattr(_lib.lib(), f"gbdpcg_solve_batched_host_{suf}")
-    _lib.check(f(None, _host(h_S, h_S.dtype, ms, "h_S"),
+    _lib.check(f(_ws(workspace), _host(h_S, h_S.dtype, ms, "h_S"),
                  None if h_Pinv is None else _host(h_Pinv, h_S.dtype, ms, "h_Pinv"),
                  _host(h_gamma, h_S.dtype, vs, "h_gamma"), _host(h_lambda, h_S.dtype, vs, "h_lambda", True),
                  nx, N, B, C.byref(cfg), iters.ctypes.data_as(C.c_void_p), exits.ctypes.data_as(C.c_void_p)))

@@ -16,7 +16,7 @@
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
 #include "pcg_slab.cuh"
-#include "pcg_tmem.cuh"
+#include "pcg_tmem4.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
 #include "pinv_build.h"
@@ -61,7 +61,8 @@ static constexpr size_t kMaxDynSmem = 227 * 1024;  // sm_100: 227 KB opt-in dyna
 struct Plan {
     bool generic = false;
     bool fused_kernel = false;        // second-generation kernel (pcg_fused.cuh)
-    bool tmem_kernel = false;         // tensor-memory batched kernel (pcg_tmem.cuh)
+    bool tmem_kernel = false;         // tensor-memory batched kernel (pcg_tmem.cuh / pcg_tmem4.cuh)
+    int tmem_per_sm = 0;              // CTAs of it that share an SM (tensor-memory columns, registers)
     int rpt = 1, fused = 0;           // rows per thread, single-reduction recurrence
     const RowsVariant *v = nullptr;
     int cluster = 1, bpc = 0, threads = 0, nbuf = 1, pmode = P_NONE;
@@ -184,23 +185,58 @@ static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
     return make_smem_plan<T>(v->nx, v->nxp, v->sb, bpc, nbuf).total;
 }
 
-const void *tmem_kernel_f32(int nx, const char **name);   // pcg_tmem_inst.cu
+const void *tmem_kernel_f32(int nx, const char **name);                                  // pcg_tmem_inst.cu
+const void *tmem4_kernel_f32(int nx, int variant, const char **name, int *alloc_cols);   // pcg_tmem_inst.cu
 
-// Tensor-memory batched kernel (pcg_tmem.cuh): fp32, Phi^-1 given, even nx <= 16, one CTA of <= 256 threads per system,
-// default recurrence.  Two systems per SM; worth it only when the batch fills the GPU twice over.
+// Shared memory a tensor-memory CTA asks for: at least so much that the hardware cannot place more CTAs on an SM than
+// tensor memory has columns for (a surplus CTA would sit in tcgen05.alloc until a co-resident persistent CTA has
+// finished its whole share of the batch: silent load imbalance).
+static size_t tmem_smem_request(size_t need, int per_sm)
+{
+    const size_t sm_total = 233472;                                    // 228 KB per SM, 1 KB reserved per CTA
+    const size_t floor_excl = sm_total / (size_t)(per_sm + 1);         // (per_sm + 1) x (smem + 1024) must exceed the SM
+    const size_t min_req = floor_excl > 1024 ? floor_excl - 1024 + 16 : 0;
+    return need > min_req ? need : min_req;
+}
+
+// Tensor-memory batched kernels: fp32, Phi^-1 given, even nx <= 16, one CTA per system, default recurrence.
+//   pcg_tmem4.cuh: four rows per thread, <= 128 threads per system, two CTAs per SM (four when a CTA has <= 2 warps and
+//                  <= 128 columns).  Taken when the system fits.
+//   pcg_tmem.cuh:  two rows per thread, <= 256 threads per system (GBDPCG_FLAG_TMEM_R2 forces it).
+// Worth it only when the batch fills every slot of the GPU.
 static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
 {
     if (!has_p || (nx & 1u) || nx > 16 || N < 2 || cfg.cluster > 1) return false;
     if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA)) return false;
     const char *name = nullptr;
+    if (!(cfg.flags & GBDPCG_FLAG_TMEM_R2)) {
+        int variant = 0, cols = 0;
+        if (const char *e = getenv("GBDPCG_TMEM4_VARIANT")) variant = atoi(e);                  // tuning knob (A/B runs)
+        const void *fn4 = tmem4_kernel_f32((int)nx, variant, &name, &cols);
+        const int threads4 = round_up((int)(N * ((nx + 3) / 4)), 32);
+        if (fn4 && threads4 <= kTmem4MaxThreads) {
+            int per_sm = 512 / cols;
+            const int by_regs = 65536 / (256 * threads4);                                      // __launch_bounds__(128, 2): up to 255 registers
+            if (by_regs < per_sm) per_sm = by_regs;
+            const size_t need = make_tmem4_plan((int)nx, Geo<float>::nxp((int)nx), (int)N).total;
+            if ((size_t)per_sm * (need + 1024) <= 233472) {
+                out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->tmem_per_sm = per_sm; out->v = nullptr;
+                out->cluster = 1; out->bpc = (int)N; out->threads = threads4; out->nbuf = 1; out->pmode = P_REG;
+                out->smem = tmem_smem_request(need, per_sm); out->fn = fn4; out->name = name; out->rpt = 4; out->fused = 1;
+                return true;
+            }
+        }
+    }
     const void *fn = tmem_kernel_f32((int)nx, &name);
     if (!fn) return false;
     const int threads = round_up((int)(N * nx / 2), 32);
     if (threads > kTmemMaxThreads) return false;
     const size_t smem = make_tmem_plan((int)nx, Geo<float>::nxp((int)nx), (int)N).total;
-    if ((size_t)(512 / tmem_cols(threads)) * (smem + 1024) > 233472) return false;   // as many CTAs per SM as tensor memory allows, or it is pointless
-    out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->v = nullptr; out->cluster = 1; out->bpc = (int)N;
-    out->threads = threads; out->nbuf = 1; out->pmode = P_REG; out->smem = smem; out->fn = fn; out->name = name; out->rpt = 2; out->fused = 1;
+    const int per_sm = 512 / tmem_cols(threads);
+    if ((size_t)per_sm * (smem + 1024) > 233472) return false;   // as many CTAs per SM as tensor memory allows, or it is pointless
+    out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->tmem_per_sm = per_sm; out->v = nullptr; out->cluster = 1;
+    out->bpc = (int)N; out->threads = threads; out->nbuf = 1; out->pmode = P_REG; out->smem = tmem_smem_request(smem, per_sm); out->fn = fn;
+    out->name = name; out->rpt = 2; out->fused = 1;
     return true;
 }
 
@@ -213,7 +249,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     all_variants(f64, (int)nx, &tab, &cnt);
     if (cfg.flags & GBDPCG_FLAG_TMEM) {
         if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, out)) return GBDPCG_OK; }
-        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 only (nx=%u N=%u %s)", nx, N,
+        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 threads only (nx=%u N=%u %s)", nx, N,
                     f64 ? "f64" : "f32");
     }
     // Throughput mode: a batch that fills every tensor-memory slot of the GPU (two systems per SM above 128 threads per
@@ -222,11 +258,13 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     if constexpr (!f64) {
         const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
                                   GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA;
-        // (systems of <= 64 threads lose: the register-row kernel already fits four of them on an SM -- nx=8,N=16: 0.19 vs 0.21 ms)
-        const unsigned long long per_sm = 512ull / (unsigned long long)tmem_cols(round_up((int)(N * nx / 2), 32));
-        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && (unsigned long long)batch >= per_sm * (unsigned long long)device_sms() &&
-            N * nx / 2 > 64 && plan_tmem(nx, N, has_p, cfg, out))
+        // (two-row kernel: systems of <= 64 threads lose, the register-row kernel already fits four of them on an SM -- nx=8,N=16: 0.19 vs 0.21 ms)
+        Plan tp;
+        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_tmem(nx, N, has_p, cfg, &tp) &&
+            (unsigned long long)batch >= (unsigned long long)tp.tmem_per_sm * (unsigned long long)device_sms() && (tp.rpt == 4 || N * nx / 2 > 64)) {
+            *out = tp;
             return GBDPCG_OK;
+        }
     }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
     if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
@@ -307,7 +345,7 @@ static int max_resident_problems(const Plan &p, int *out)
     }
     CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     if (p.tmem_kernel) {
-        *out = (512 / tmem_cols(p.threads)) * sms;         // 128 or 256 of the SM's 512 tensor-memory columns per CTA; plan_tmem checked shared memory and registers
+        *out = p.tmem_per_sm * sms;                        // bounded by tensor-memory columns and registers (plan_tmem), enforced through the shared-memory request
         return GBDPCG_OK;
     }
     if (p.cluster == 1) {

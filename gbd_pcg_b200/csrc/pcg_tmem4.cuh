@@ -1,0 +1,418 @@
+// pcg_tmem4.cuh -- batched fp32 solver, FOUR rows per thread: two systems resident per SM, one CTA of <= 4 warps each,
+// S in registers, Phi^-1 in TENSOR MEMORY.  Second generation of pcg_tmem.cuh (two rows per thread, 7-8 warps per system).
+//
+// Why four rows.  ncu of the two-row kernel on C5 (profiles/ncu_tmem_r1g.txt): shared-memory wavefronts 69 % of peak, FP32 pipe
+// 32 %, issue 36 % -- the binding path is the window read-back (every thread loads the 3*nx window entries of its block-row
+// per mat-vec, 128 B/clk/SM whether lanes broadcast or not), and its cost is  threads x 3nx x 4 B  per mat-vec, i.e. inversely
+// proportional to the rows a thread owns.  With four rows a C2 system is 32 block-rows x 4 threads = 128 threads = 4 warps,
+// one per tensor-memory lane quarter, and a window quad read from shared memory feeds 8 packed FMAs instead of 4.
+//
+// Ownership.  Block-row b is owned by G = ceil(nx/4) consecutive threads; thread g of the group owns rows 4g .. 4g+3 of the
+// block-row (rows >= nx of the last thread are padding: zero matrix rows, never published).  nx = 14: 4 threads per block-row,
+// the fourth with two real rows (1/8 of the FMA lanes idle; nx = 12, 16: none).  A "quad" is four consecutive columns of one of
+// the three blocks of a block-row (the last quad of a block has two columns when nx = 2 mod 4); a thread's share of one matrix
+// is 3*NQ quads x 4 rows.
+//
+// Where the matrices live (per thread): all of S (12 quads, 168 values for nx = 14) in registers except the last SQT quads,
+// Phi^-1 in tensor memory except its first PQR quads.  A quad in tensor memory is one tcgen05.ld.32x32b.x16 (x8 for a half
+// quad): lane = thread, so the data is thread-private; register [row*W + e] of the chunk is m(row, 4i+e).  The three on-chip
+// sources are then balanced for nx = 14 (two co-resident iterations): FP32 pipe 2 x 2 x 84 FFMA2 x 2 clk = 672 clk per
+// sub-partition, tensor-memory reads 2 x 168 columns x 128 lanes x 4 B / 256 B/clk = 672 clk, window reads 2 x 2 x 168 = 672
+// wavefronts -- against 2 x 588 wavefronts + 2 x 420 clk of LDTM in the two-row kernel, whose two co-resident iterations take ~2200 clk.
+//
+// Same recurrence as pcg_tmem.cuh / pcg_fused.cuh (single-reduction Chronopoulos-Gear form of reference include/pcg.cuh:118-212),
+// same exit test (pcg.cuh:195), same output semantics (pcg.cuh:212-215).  The accumulation chains differ from the two-row
+// kernels (one packed chain per row, columns in ascending order), so lambda agrees with them to rounding, not bit for bit;
+// parity is held against the host oracle (tests/test_parity_gpu.py::test_tmem4_*).
+#pragma once
+#include <type_traits>
+
+#include "pcg_tmem.cuh"
+
+#ifndef TMEM4_L2_PREFETCH
+#define TMEM4_L2_PREFETCH 1   // pull the next system's S into L2 behind the iterations (its bulk copy into the one staging buffer is exposed)
+#endif
+
+namespace gbdpcg {
+
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%8], {%0,%1,%2,%3,%4,%5,%6,%7};" ::"r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]),
+                 "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(taddr)
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld8(uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7])
+                 :
+                 : "memory");
+}
+__device__ __forceinline__ void l2_prefetch_bulk(const void *src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
+// compile-time geometry of a thread's share
+template <int NX, int SQT, int PQR>
+struct T4Geo {
+    static constexpr int G = (NX + 3) / 4;       // threads per block-row = quads per block
+    static constexpr int NQ = G, NQT = 3 * NQ;   // quads per block, per block-row
+    __host__ __device__ static constexpr int qw(int q) { return (NX - 4 * (q % NQ) >= 4) ? 4 : NX - 4 * (q % NQ); }   // columns of quad q: 4 or 2
+    __host__ __device__ static constexpr bool p_tmem(int q) { return q >= PQR; }
+    __host__ __device__ static constexpr bool s_tmem(int q) { return q >= NQT - SQT; }
+    __host__ __device__ static constexpr bool in_tmem(bool is_s, int q) { return is_s ? s_tmem(q) : p_tmem(q); }
+    __host__ __device__ static constexpr int count(bool is_s, bool tm)
+    {
+        int n = 0;
+        for (int q = 0; q < NQT; q++) n += (in_tmem(is_s, q) == tm) ? 1 : 0;
+        return n;
+    }
+    // k-th quad of matrix is_s that lives in tensor memory (tm) / registers (!tm)
+    __host__ __device__ static constexpr int nth(bool is_s, bool tm, int k)
+    {
+        for (int q = 0; q < NQT; q++)
+            if (in_tmem(is_s, q) == tm) {
+                if (k == 0) return q;
+                k--;
+            }
+        return -1;
+    }
+    // tensor-memory column of quad q: Phi^-1 quads first, then the S quads
+    __host__ __device__ static constexpr int col(bool is_s, int q)
+    {
+        int c = 0;
+        for (int k = 0; k < NQT; k++)
+            if (p_tmem(k) && (is_s || k < q)) c += 4 * qw(k);
+        if (is_s)
+            for (int k = 0; k < q; k++)
+                if (s_tmem(k)) c += 4 * qw(k);
+        return c;
+    }
+    static constexpr int cols = col(true, NQT);
+    static constexpr int alloc_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : 256;
+};
+
+struct Tmem4Plan {
+    uint32_t mbar_off, tbase_off, red_off, winA_off, winB_off, stage_off, total;
+};
+__host__ __device__ inline Tmem4Plan make_tmem4_plan(int nx, int nxp, int N)
+{
+    Tmem4Plan p;
+    uint32_t o = 0;
+    p.mbar_off = o;  o += 16;
+    p.tbase_off = o; o += 16;
+    p.red_off = o;   o += 2 * 8 * 4;                                     // 2 slots x 4 warps x (gamma, delta)
+    p.winA_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
+    p.winB_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
+    p.stage_off = o; o += (uint32_t)round_up(N * 3 * nx * nx * 4, 16);   // ONE matrix at a time
+    p.total = o;
+    return p;
+}
+constexpr int kTmem4MaxThreads = 128;    // 4 warps: one per tensor-memory lane quarter
+
+// ---- a thread's share of one matrix, quad by quad (compile-time recursion over the quad index) ----
+// the 4 rows x W columns of quad Q from the staged block-row image (column-major nx x 3nx panel); rowp = first row of this thread
+template <class GEO, int NX, int Q>
+__device__ __forceinline__ void t4_gather_quad(const float *rowp, bool hi_ok, bool kill, float (&m)[4][4])
+{
+    constexpr int j = Q / GEO::NQ, i = Q % GEO::NQ, W = GEO::qw(Q);
+#pragma unroll
+    for (int e = 0; e < W; e++) {
+        const float *src = rowp + (j * NX + 4 * i + e) * NX;
+        const float2 lo = *reinterpret_cast<const float2 *>(src);
+        float2 hi = make_float2(0.f, 0.f);
+        if (hi_ok) hi = *reinterpret_cast<const float2 *>(src + 2);
+        m[0][e] = kill ? 0.f : lo.x;
+        m[1][e] = kill ? 0.f : lo.y;
+        m[2][e] = kill ? 0.f : hi.x;
+        m[3][e] = kill ? 0.f : hi.y;
+    }
+}
+// staging -> registers (Mr[q]) or tensor memory (chunk register [row*W + e] = m(row, e)), quads Q .. NQT-1
+template <class GEO, int NX, bool IS_S, int Q>
+__device__ __forceinline__ void t4_load_matrix(const float *rowp, bool hi_ok, bool kill_left, bool kill_mid, bool kill_right, uint32_t tmine,
+                                               float (&Mr)[GEO::NQT][4][4])
+{
+    if constexpr (Q < GEO::NQT) {
+        constexpr int j = Q / GEO::NQ, W = GEO::qw(Q);
+        const bool kill = (j == 0) ? kill_left : (j == 2) ? kill_right : kill_mid;
+        if constexpr (GEO::in_tmem(IS_S, Q)) {
+            float m[4][4];
+            t4_gather_quad<GEO, NX, Q>(rowp, hi_ok, kill, m);
+            uint32_t v[16];
+#pragma unroll
+            for (int row = 0; row < 4; row++)
+#pragma unroll
+                for (int e = 0; e < W; e++) v[row * W + e] = __float_as_uint(m[row][e]);
+            if constexpr (W == 4) tmem_st16(tmine + GEO::col(IS_S, Q), v);
+            else tmem_st8(tmine + GEO::col(IS_S, Q), v);
+        } else {
+            t4_gather_quad<GEO, NX, Q>(rowp, hi_ok, kill, Mr[Q]);
+        }
+        t4_load_matrix<GEO, NX, IS_S, Q + 1>(rowp, hi_ok, kill_left, kill_mid, kill_right, tmine, Mr);
+    }
+}
+// window quad Q (16-byte load, 8-byte for a half quad) and its packed multiply-adds: acc[row] += m(row, 0..W-1) . x(0..W-1)
+template <class GEO, int NXP, int Q>
+__device__ __forceinline__ float4 t4_window_quad(const float *w)
+{
+    constexpr int j = Q / GEO::NQ, i = Q % GEO::NQ;
+    if constexpr (GEO::qw(Q) == 4) return *reinterpret_cast<const float4 *>(w + j * NXP + 4 * i);
+    else {
+        const float2 h = *reinterpret_cast<const float2 *>(w + j * NXP + 4 * i);
+        return make_float4(h.x, h.y, 0.f, 0.f);
+    }
+}
+template <class GEO, int NXP, int Q>
+__device__ __forceinline__ void t4_fma_reg(const float (&m)[4][4], const float *w, float2 (&acc)[4])
+{
+    const float4 x = t4_window_quad<GEO, NXP, Q>(w);
+#pragma unroll
+    for (int row = 0; row < 4; row++) acc[row] = __ffma2_rn(make_float2(m[row][0], m[row][1]), make_float2(x.x, x.y), acc[row]);
+    if constexpr (GEO::qw(Q) == 4) {
+#pragma unroll
+        for (int row = 0; row < 4; row++) acc[row] = __ffma2_rn(make_float2(m[row][2], m[row][3]), make_float2(x.z, x.w), acc[row]);
+    }
+}
+template <class GEO, int NXP, int Q>
+__device__ __forceinline__ void t4_fma_tm(const uint32_t (&u)[16], const float *w, float2 (&acc)[4])
+{
+    constexpr int W = GEO::qw(Q);
+    const float4 x = t4_window_quad<GEO, NXP, Q>(w);
+#pragma unroll
+    for (int row = 0; row < 4; row++)
+        acc[row] = __ffma2_rn(make_float2(__uint_as_float(u[row * W]), __uint_as_float(u[row * W + 1])), make_float2(x.x, x.y), acc[row]);
+    if constexpr (W == 4) {
+#pragma unroll
+        for (int row = 0; row < 4; row++)
+            acc[row] = __ffma2_rn(make_float2(__uint_as_float(u[row * W + 2]), __uint_as_float(u[row * W + 3])), make_float2(x.z, x.w), acc[row]);
+    }
+}
+template <class GEO, bool IS_S, int K>
+__device__ __forceinline__ void t4_tmem_ld(uint32_t tmine, uint32_t (&u)[16])
+{
+    if constexpr (K < GEO::count(IS_S, true)) {
+        constexpr int q = GEO::nth(IS_S, true, K);
+        if constexpr (GEO::qw(q) == 4) tmem_ld16(tmine + GEO::col(IS_S, q), u);
+        else tmem_ld8(tmine + GEO::col(IS_S, q), u);
+    }
+}
+// Step K of a mat-vec: the K-th register quad, then the K-th tensor-memory quad (wait for its chunk `cur`, start the next
+// chunk into `nxt`, multiply).  The chunks are double-buffered; the caller loads chunk 0 BEFORE the barrier that publishes
+// the vector, so its latency hides behind the barrier.
+template <class GEO, int NXP, bool IS_S, int K>
+__device__ __forceinline__ void t4_mv_step(const float (&Mr)[GEO::NQT][4][4], const float *w, uint32_t tmine, uint32_t (&cur)[16],
+                                           uint32_t (&nxt)[16], float2 (&acc)[4])
+{
+    constexpr int nT = GEO::count(IS_S, true), nR = GEO::count(IS_S, false), nK = nT > nR ? nT : nR;
+    if constexpr (K < nK) {
+        if constexpr (K < nR) {
+            constexpr int q = GEO::nth(IS_S, false, K);
+            t4_fma_reg<GEO, NXP, q>(Mr[q], w, acc);
+        }
+        if constexpr (K < nT) {
+            constexpr int q = GEO::nth(IS_S, true, K);
+            if constexpr (GEO::qw(q) == 4) tmem_wait_ld(cur);
+            else tmem_wait_ld8(cur);
+            t4_tmem_ld<GEO, IS_S, K + 1>(tmine, nxt);
+            t4_fma_tm<GEO, NXP, q>(cur, w, acc);
+        }
+        t4_mv_step<GEO, NXP, IS_S, K + 1>(Mr, w, tmine, nxt, cur, acc);
+    }
+}
+
+template <int NX, int SQT, int PQR>
+__global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const KernelArgs<float> a)
+{
+    static_assert(NX % 2 == 0 && NX >= 4 && NX <= 16, "even state sizes up to 16");
+    using T = float;
+    using GEO = T4Geo<NX, SQT, PQR>;
+    constexpr int R = 4, G = GEO::G, NQT = GEO::NQT, BSZ = 3 * NX * NX, NXP = Geo<T>::nxp(NX);
+    static_assert(GEO::cols <= 256, "a thread's tensor-memory columns (two CTAs share the SM's 512)");
+    static_assert(NXP >= 4 * G, "a thread publishes four window entries");
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int N = (int)a.N;
+    const Tmem4Plan plan = make_tmem4_plan(NX, NXP, N);
+    T *red = reinterpret_cast<T *>(smem_raw + plan.red_off);
+    T *winA = reinterpret_cast<T *>(smem_raw + plan.winA_off);
+    T *winB = reinterpret_cast<T *>(smem_raw + plan.winB_off);
+    T *stage = reinterpret_cast<T *>(smem_raw + plan.stage_off);
+    uint32_t *tbase_s = reinterpret_cast<uint32_t *>(smem_raw + plan.tbase_off);
+    const uint32_t mbar = smem_u32(smem_raw + plan.mbar_off);
+
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const int lb = t / G, g = t - lb * G;
+    const bool active = lb < N;
+    const bool hi_ok = active && (4 * g + 2 < NX);         // rows 4g+2, 4g+3 exist
+    const int b = lb;
+
+    for (int i = t; i < (N + 2) * NXP; i += blockDim.x) { winA[i] = 0.f; winB[i] = 0.f; }
+    if (t < 16) red[t] = 0.f;
+    if (t == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(GEO::alloc_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tbase = *tbase_s;
+    const uint32_t tmine = tbase + ((uint32_t)(32 * warp) << 16);
+
+    const int slot = (lb + 1) * NXP + 4 * g;
+    const int wofs = (active ? lb : 0) * NXP;
+    auto publish = [&](T *win, const T (&x)[R]) {
+        if (active) *reinterpret_cast<float4 *>(win + slot) = make_float4(x[0], x[1], x[2], x[3]);   // padding rows hold 0
+    };
+    int red_slot = 0;
+    auto all_sum = [&](T x0, T x1) -> Pair<T> {
+        Pair<T> p(x0, x1);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) p = p + shfl_xor_pair<T>(p, o);
+        T *rd = red + red_slot * 8;
+        if (lane == 0) *reinterpret_cast<float2 *>(rd + 2 * warp) = make_float2(p.x(), p.y());
+        __syncthreads();
+        Pair<T> s = pair_tree_sum<T, 4>(rd);
+        red_slot ^= 1;
+        return s;
+    };
+
+    const uint32_t mat_bytes = (uint32_t)(N * BSZ * (int)sizeof(T));
+    auto issue_copy = [&](const T *src) {
+        mbar_expect_tx(mbar, mat_bytes);
+        bulk_g2s(smem_u32(stage), src, mat_bytes, mbar);
+    };
+    uint32_t phase = 0;
+    if (t == 0 && blockIdx.x < a.batch) issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride);
+
+    const bool kill_left = !active || b == 0, kill_right = !active || b == N - 1, kill_mid = !active;
+    const T *rowp = stage + (active ? lb * BSZ + 4 * g : 0);
+
+    for (uint32_t prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
+        const size_t vofs = (size_t)prob * a.vec_stride + (size_t)b * NX + 4 * g;
+        T lam[R] = {0.f, 0.f, 0.f, 0.f}, gam[R] = {0.f, 0.f, 0.f, 0.f};
+        if (active) {
+            lam[0] = a.lambda[vofs]; lam[1] = a.lambda[vofs + 1];
+            gam[0] = __ldg(a.gamma + vofs); gam[1] = __ldg(a.gamma + vofs + 1);
+            if (hi_ok) {
+                lam[2] = a.lambda[vofs + 2]; lam[3] = a.lambda[vofs + 3];
+                gam[2] = __ldg(a.gamma + vofs + 2); gam[3] = __ldg(a.gamma + vofs + 3);
+            }
+        }
+
+        // ---- Phi^-1: staging -> tensor memory (registers for its first PQR quads) ----
+        T Pr[NQT][4][4], Sr[NQT][4][4];               // only the quads that stay in registers are ever touched
+        mbar_wait(mbar, phase); phase ^= 1;
+        t4_load_matrix<GEO, NX, false, 0>(rowp, hi_ok, kill_left, kill_mid, kill_right, tmine, Pr);
+        __syncthreads();                                   // every thread has read its Phi^-1 rows: staging is free
+        if (t == 0) { fence_proxy_async(); issue_copy(a.S + (size_t)prob * a.mat_stride); }
+
+        // ---- S: staging -> registers (tensor memory for its last SQT quads) ----
+        mbar_wait(mbar, phase); phase ^= 1;
+        t4_load_matrix<GEO, NX, true, 0>(rowp, hi_ok, kill_left, kill_mid, kill_right, tmine, Sr);
+        tmem_wait_st();
+        __syncthreads();                                   // staging is free again: fetch the next system's Phi^-1 behind the iterations
+        {
+            const uint32_t next = prob + gridDim.x;
+            if (t == 0 && next < a.batch) {
+                fence_proxy_async();
+                issue_copy(a.Pinv + (size_t)next * a.mat_stride);
+#if TMEM4_L2_PREFETCH
+                l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
+#endif
+            }
+        }
+
+        // y = M * window for this thread's four rows: quads in registers and quads in tensor memory alternate (t4_mv_step)
+        auto finish = [&](const float2 (&acc)[R], T (&y)[R]) {
+            y[0] = active ? acc[0].x + acc[0].y : 0.f;
+            y[1] = active ? acc[1].x + acc[1].y : 0.f;
+            y[2] = hi_ok ? acc[2].x + acc[2].y : 0.f;
+            y[3] = hi_ok ? acc[3].x + acc[3].y : 0.f;
+        };
+        auto mv_S = [&](const T *win, uint32_t (&ua)[16], T (&y)[R]) {
+            uint32_t ub[16];
+            float2 acc[R] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+            t4_mv_step<GEO, NXP, true, 0>(Sr, win + wofs, tmine, ua, ub, acc);
+            finish(acc, y);
+        };
+        auto mv_P = [&](const T *win, uint32_t (&ua)[16], T (&y)[R]) {
+            uint32_t ub[16];
+            float2 acc[R] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+            t4_mv_step<GEO, NXP, false, 0>(Pr, win + wofs, tmine, ua, ub, acc);
+            finish(acc, y);
+        };
+
+        // ---- r = gamma - S*lambda                                               (pcg.cuh:118-126) ----
+        T res[R], rt[R], w[R], p[R], s[R];
+        uint32_t u0[16];
+        publish(winB, lam);
+        t4_tmem_ld<GEO, true, 0>(tmine, u0);
+        __syncthreads();
+        mv_S(winB, u0, w);
+#pragma unroll
+        for (int i = 0; i < R; i++) { res[i] = gam[i] - w[i]; p[i] = 0.f; s[i] = 0.f; }
+
+        uint32_t it = 0;
+        bool hit_max = true;
+        T rcp_gamma = 0.f, rcp_alpha = 0.f;
+        for (;;) {
+            publish(winA, res);
+            t4_tmem_ld<GEO, false, 0>(tmine, u0);
+            __syncthreads();
+            mv_P(winA, u0, rt);                   // r~ = Phi^-1 r                (pcg.cuh:131-140, 181-184)
+            publish(winB, rt);
+            t4_tmem_ld<GEO, true, 0>(tmine, u0);
+            __syncthreads();
+            mv_S(winB, u0, w);                       // w = S r~
+            T gg = 0.f, dd = 0.f;
+#pragma unroll
+            for (int i = 0; i < R; i++) { gg += res[i] * rt[i]; dd += w[i] * rt[i]; }
+            const Pair<T> gd = all_sum(gg, dd);            // gamma = r.r~ , delta = w.r~
+            const T gamma = gd.x(), delta = gd.y();
+            if (it > 0 && abs_t(gamma) < a.tol) { hit_max = false; break; }   // reference exit test (pcg.cuh:195)
+            if (it == a.max_iter) break;
+            T beta, alpha;
+            if (it == 0) { beta = 0.f; alpha = gamma / delta; }
+            else {
+                beta = gamma * rcp_gamma;
+                alpha = gamma / (delta - beta * (gamma * rcp_alpha));
+            }
+#pragma unroll
+            for (int i = 0; i < R; i++) {
+                p[i] = rt[i] + beta * p[i];
+                lam[i] += alpha * p[i];
+                s[i] = w[i] + beta * s[i];
+                res[i] -= alpha * s[i];
+            }
+            rcp_gamma = 1.f / gamma;
+            rcp_alpha = 1.f / alpha;
+            ++it;
+        }
+
+        // ---- outputs                                                            (pcg.cuh:212-215) ----
+        if (active) {
+            a.lambda[vofs] = lam[0]; a.lambda[vofs + 1] = lam[1];
+            if (hi_ok) { a.lambda[vofs + 2] = lam[2]; a.lambda[vofs + 3] = lam[3]; }
+        }
+        if (t == 0) {
+            if (a.iters) a.iters[prob] = it;
+            if (a.exits) a.exits[prob] = hit_max ? 1 : 0;
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(GEO::alloc_cols) : "memory");
+}
+
+}  // namespace gbdpcg

@@ -1,5 +1,6 @@
-// pcg_tmem_inst.cu -- instantiations of the tensor-memory batched solver (pcg_tmem.cuh), fp32, even state sizes <= 16.
-#include "pcg_tmem.cuh"
+// pcg_tmem_inst.cu -- instantiations of the tensor-memory batched solvers, fp32, even state sizes <= 16:
+// pcg_tmem.cuh (two rows per thread, up to 8 warps per system) and pcg_tmem4.cuh (four rows per thread, up to 4 warps).
+#include "pcg_tmem4.cuh"
 
 namespace gbdpcg {
 
@@ -11,6 +12,27 @@ const void *tmem_kernel_f32(int nx, const char **name)
 #undef CASE
     default: *name = nullptr; return nullptr;
     }
+}
+
+// Four rows per thread.  `variant` picks where a thread's quads live: (SQT, PQR) = S quads in tensor memory, Phi^-1 quads in
+// registers.  Variant 0 is what the planner uses; the others are kept for A/B runs (GBDPCG_TMEM4_VARIANT, scripts/bench_variants.py).
+const void *tmem4_kernel_f32(int nx, int variant, const char **name, int *alloc_cols)
+{
+#define V(NX, ID, SQT, PQR)                                                                 \
+    if (nx == NX && variant == ID) {                                                        \
+        *name = "pcg_tmem4<f32,nx=" #NX ",R=4,S_tmem=" #SQT ",P_reg=" #PQR ",2 per SM>";    \
+        *alloc_cols = T4Geo<NX, SQT, PQR>::alloc_cols;                                      \
+        return (const void *)pcg_tmem4_kernel<NX, SQT, PQR>;                                \
+    }
+    V(8, 0, 0, 0)
+    V(10, 0, 0, 0)
+    V(12, 0, 0, 0) V(12, 1, 3, 3)
+    V(14, 0, 0, 0) V(14, 1, 4, 0) V(14, 2, 6, 6) V(14, 3, 3, 3) V(14, 4, 2, 0)
+    V(16, 0, 4, 0) V(16, 1, 6, 2)
+#undef V
+    *name = nullptr;
+    *alloc_cols = 0;
+    return nullptr;
 }
 
 }  // namespace gbdpcg

@@ -73,8 +73,12 @@ typedef struct gbdpcg_config {
  * the Pinv argument and empty_pinv are then ignored.  This is what makes the reference's own host signature
  * solvePCG<T>(h_S, h_gamma, h_lambda, ...) -- which has no Pinv parameter (include/interface.cuh:24-31) -- a
  * PRECONDITIONED solve, and it halves the bytes a host-resident batch has to push over PCIe. */
-#define GBDPCG_FLAG_TMEM 0x400u         /* fp32 batched: two (or, up to 128 threads per system, four) systems per SM, Phi^-1 and the right blocks of S in tensor memory
-                                           (pcg_tmem.cuh); GBDPCG_ERR_UNSUPPORTED for shapes it does not cover */
+#define GBDPCG_FLAG_TMEM 0x400u         /* fp32 batched: two (small systems: four) systems per SM with Phi^-1 in tensor memory (pcg_tmem4.cuh: four rows per
+                                           thread, S in registers; pcg_tmem.cuh: two rows per thread for systems of more than 128 such threads);
+                                           GBDPCG_ERR_UNSUPPORTED for shapes neither covers.  Assumes no other tensor-memory user (e.g. a concurrent
+                                           tcgen05 GEMM on another stream) shares the SMs: tcgen05.alloc blocks until columns are free */
+#define GBDPCG_FLAG_TMEM_R2 0x1000u     /* with GBDPCG_FLAG_TMEM or the planner's own choice: the two-rows-per-thread tensor-memory kernel (pcg_tmem.cuh) even where the
+                                           four-rows-per-thread one (pcg_tmem4.cuh, systems of up to 128 threads) applies -- A/B measurements */
 #define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick the tensor-memory kernel (the planner takes it for fp32 batches that fill its 2 or 4 slots per SM) */
 #define GBDPCG_FLAG_BUILD_JACOBI 0x100u
 #define GBDPCG_FLAG_BUILD_STAIR 0x200u

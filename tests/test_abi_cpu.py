@@ -117,7 +117,7 @@ def test_invalid_arguments_are_rejected_before_any_cuda_call():
 
 
 @pytest.mark.skipif(shutil.which("nvcc") is None, reason="needs nvcc")
-@pytest.mark.parametrize("example", ["pcg_solve.cu", "pcg_solve_dp.cu", "pcg_solve_csr.cu"])
+@pytest.mark.parametrize("example", ["pcg_solve.cu", "pcg_solve_dp.cu", "pcg_solve_csr.cu", "api_surface.cu"])
 def test_reference_style_example_compiles_against_the_new_headers(example, tmp_path):
     """Acceptance of the header shim: a program written against the reference's
     gpu_pcg.cuh / solvePCG<T> builds with -I include -lgbdpcg.  Uses the reference's own example where the
@@ -125,8 +125,11 @@ def test_reference_style_example_compiles_against_the_new_headers(example, tmp_p
     ref = os.path.join("/root/reference/examples", example)
     src = ref if os.path.exists(ref) else os.path.join(ROOT, "examples", example)
     exe = tmp_path / "a.out"
-    subprocess.check_call(["nvcc", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I", os.path.join(ROOT, "include"), src,
-                           "-L", os.path.dirname(_lib.LIB_PATH), "-lgbdpcg", "-o", str(exe)])
+    # api_surface.cu instantiates the rest of the template surface: overload 3 with scratch buffers, pcg_solve<T> with the config
+    # defaulted, pcgSharedMemSize<T>, checkPcgOccupancy<T> (uninstantiated templates are not even type-checked)
+    subprocess.check_call(["nvcc", "-std=c++17", "-Wno-deprecated-gpu-targets", "-I", os.path.join(ROOT, "include"), "-I",
+                           os.path.join(ROOT, "examples"), src, "-L", os.path.dirname(_lib.LIB_PATH), "-lgbdpcg", "-Xcompiler", "-pthread",
+                           "-o", str(exe)])
     if not _cuda_ok():
         env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(_lib.LIB_PATH) + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
         r = subprocess.run([str(exe)], env=env, capture_output=True, text=True)

@@ -476,7 +476,13 @@ def test_against_reference_cuda(name, dtype, precond):
     assert abs(it - it_r) <= 1, (it, it_r)
     if it == it_r:
         assert ex == ex_r
-        assert rel_err(lam, lam_r) <= LAMBDA_TOL[np.dtype(dtype)]
+    else:
+        # equal iteration count: both kernels again, capped at the smaller count (max_iter exit, the test can no longer fire first)
+        k = min(it, it_r)
+        lam_r, it_r2, _ = ref_cuda.get(dtype, nx, N).solve(S, P_ref, gam, lam0, k, tol)
+        lam, it2, _ = gpu_solve(S, P, gam, lam0, nx, N, tol, k)
+        assert it2 == k and it_r2 == k
+    assert rel_err(lam, lam_r) <= LAMBDA_TOL[np.dtype(dtype)]
 
 
 def test_golden_reference_fixtures():
@@ -493,9 +499,15 @@ def test_golden_reference_fixtures():
         lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
         if name == "C1" and dtype == np.float32:
             continue
-        assert abs(it - int(z["iters"])) <= 1
-        if it == int(z["iters"]):
-            assert rel_err(lam, z["lam"]) <= LAMBDA_TOL[dtype], f
+        it_ref = int(z["iters"])
+        assert abs(it - it_ref) <= 1
+        if it > it_ref:        # equal iteration count: this kernel again, capped at the recorded count
+            lam, it, _ = gpu_solve(S, P, gam, lam0, nx, N, tol, it_ref)
+        elif it < it_ref:      # the recorded run went one further: the oracle (held to the same fixture on the CPU) bridges the step
+            lam_o = oracle.pcg(S, P, gam, lam0, nx, N, 0.0, it, order=0)[0]
+            assert rel_err(lam, lam_o) <= LAMBDA_TOL[dtype], f
+            continue
+        assert it == it_ref and rel_err(lam, z["lam"]) <= LAMBDA_TOL[dtype], f
 
 
 # ---------------------------------------------------------------------------------------------
@@ -518,6 +530,60 @@ def test_cpp_examples_run(example, iters, tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     m = re.search(r"(\d+) iterations", r.stdout)
     assert m and (iters is None or int(m.group(1)) == iters), r.stdout
+
+
+def test_cpp_api_surface(tmp_path):
+    """examples/api_surface.cu, compiled and RUN: overload 3 with real scratch buffers (reference include/interface.cuh:92-103),
+    pcg_solve<T> with the config defaulted (README.md:42), pcgSharedMemSize<T> / checkPcgOccupancy<T> (include/pcg.cuh:13-49), and
+    two host threads with their own gbdpcg_workspace and stream solving different systems concurrently -- all against known answers."""
+    import shutil
+    import subprocess
+    from conftest import ROOT
+    if shutil.which("nvcc") is None:
+        pytest.skip("needs nvcc")
+    libdir = os.path.join(ROOT, "gbd_pcg_b200")
+    exe = tmp_path / "api_surface"
+    subprocess.check_call(["nvcc", "-std=c++17", "-O2", "-Wno-deprecated-gpu-targets", "-I", os.path.join(ROOT, "include"), "-I",
+                           os.path.join(ROOT, "examples"), os.path.join(ROOT, "examples", "api_surface.cu"), "-L", libdir, "-lgbdpcg",
+                           "-Xcompiler", "-pthread", "-o", str(exe)])
+    env = dict(os.environ, LD_LIBRARY_PATH=libdir + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    r = subprocess.run([str(exe)], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "all checks passed" in r.stdout, r.stdout + r.stderr
+    assert "two threads, own workspace + stream each: 80 + 80 solves, failures 0 + 0" in r.stdout
+
+
+def test_python_mirror_workspace_handle():
+    """gbdpcg_workspace_create / _destroy through the Python mirror: two workspaces on two host threads, host and device entry points."""
+    import threading
+    torch = _torch()
+    out = {}
+
+    def work(tag, name, precond):
+        S, P, gam, nx, N, tol, max_iter = make_system(name, precond)
+        cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0)
+        with g.workspace() as ws:
+            res = []
+            for _ in range(20):
+                lam = np.zeros(N * nx, dtype=S.dtype)
+                it = g.solvePCG(S, gam, lam, nx, N, cfg, h_Pinv=P, workspace=ws)
+                res.append((it, lam.copy()))
+            st = torch.cuda.Stream()
+            d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (S, P, gam))
+            d_l = torch.zeros(N * nx, dtype=d_S.dtype, device="cuda")
+            torch.cuda.synchronize()
+            it_d = g.api._solve_dev(nx, N, d_S, d_P, d_g, d_l, config=cfg, workspace=ws, stream=st)
+            out[tag] = (res, it_d, d_l.cpu().numpy(), (S, P, gam, nx, N, tol, max_iter))
+
+    ts = [threading.Thread(target=work, args=("a", "C2", "stair")), threading.Thread(target=work, args=("b", "C3", "jacobi"))]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    for tag in ("a", "b"):
+        res, it_d, lam_d, (S, P, gam, nx, N, tol, max_iter) = out[tag]
+        lam0 = np.zeros(N * nx, dtype=S.dtype)
+        for it, lam in res:
+            assert it == res[0][0] and np.array_equal(lam, res[0][1])
+        check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, res[0][1], res[0][0], False)
+        assert it_d == res[0][0] and np.array_equal(lam_d, res[0][1])
 
 
 # ---------------------------------------------------------------------------------------------
@@ -566,13 +632,18 @@ def _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags):
     return d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
 
 
+TMEM_ARMS = {"r4": lambda: g._lib.FLAG_TMEM, "r2": lambda: g._lib.FLAG_TMEM | g._lib.FLAG_TMEM_R2}
+
+
 @pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 32, 700), (14, 7, 32, 5), (12, 4, 40, 301), (16, 8, 30, 297), (8, 4, 60, 330), (10, 5, 17, 1000),
                                            (14, 7, 2, 64), (16, 8, 32, 40), (16, 8, 16, 1300), (8, 4, 30, 2000), (12, 6, 20, 777)])
 @pytest.mark.parametrize("precond", ["stair", "jacobi"])
-def test_tmem_kernel_vs_oracle_and_register_kernel(nx, nu, N, batch, precond):
+@pytest.mark.parametrize("arm", ["r4", "r2"])
+def test_tmem_kernel_vs_oracle_and_register_kernel(nx, nu, N, batch, precond, arm):
     """GBDPCG_FLAG_TMEM on ragged batch sizes (fewer systems than CTAs, not a multiple of the grid), the smallest and the
-    largest supported system: every system against the host oracle; against the register-row kernel bit for bit where
-    both reduce over the same number of warp slots."""
+    largest supported system: every system against the host oracle.  Arm r4 = four rows per thread (pcg_tmem4.cuh) where the
+    system fits 128 such threads; arm r2 = two rows per thread (pcg_tmem.cuh), bit for bit equal to the register-row kernel
+    where both reduce over the same number of warp slots."""
     torch = _torch()
     nseed = 6
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), precond, np.float32)
@@ -581,12 +652,15 @@ def test_tmem_kernel_vs_oracle_and_register_kernel(nx, nu, N, batch, precond):
     d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (Sb, Pb, gb))
     lam0 = np.zeros((batch, N * nx), np.float32)
     tol, max_iter = 1e-6, 1000
-    assert "pcg_tmem" in g.plan_query(nx, N, np.float32, True, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=batch)["kernel"]
-    lam_t, it_t, ex_t = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, g._lib.FLAG_TMEM)
+    flags = TMEM_ARMS[arm]()
+    kern = g.plan_query(nx, N, np.float32, True, g.pcg_config(flags=flags), batch=batch)["kernel"]
+    four = N * ((nx + 3) // 4) <= 128 and arm == "r4"
+    assert ("pcg_tmem4" in kern) if four else ("pcg_tmem<" in kern)
+    lam_t, it_t, ex_t = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags)
     lam_r, it_r, ex_r = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, g._lib.FLAG_NO_TMEM)
     assert not ex_t.any()
     assert np.abs(it_t.astype(int) - it_r.astype(int)).max() <= 1
-    if nx in (12, 14, 16) and N * nx // 2 > 128:
+    if not four and nx in (12, 14, 16) and N * nx // 2 > 128:
         assert np.array_equal(it_t, it_r) and np.array_equal(lam_t.view(np.uint32), lam_r.view(np.uint32))
     for s in range(min(nseed, batch)):
         idx = np.arange(s, batch, nseed)
@@ -594,9 +668,11 @@ def test_tmem_kernel_vs_oracle_and_register_kernel(nx, nu, N, batch, precond):
         check_against_oracle(S[s], P[s], gam[s], np.zeros(N * nx, np.float32), nx, N, tol, max_iter, lam_t[s], int(it_t[s]), bool(ex_t[s]))
 
 
-def test_tmem_kernel_edge_semantics():
+@pytest.mark.parametrize("arm", ["r4", "r2"])
+def test_tmem_kernel_edge_semantics(arm):
     """max_iter = 0 leaves lambda, a low cap reports the flag, warm starts, padding blocks never reach the arithmetic."""
     torch = _torch()
+    fl = TMEM_ARMS[arm]()
     nx, nu, N, batch = 14, 7, 32, 300
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(4), "stair", np.float32)
     Sb, Pb, gb = (np.tile(a, (batch // 4, 1)).copy() for a in (S, P, gam))
@@ -607,13 +683,15 @@ def test_tmem_kernel_edge_semantics():
         M[:, (N - 1) * 3 * nx * nx + 2 * nx * nx:] = np.nan
     d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (Sb, Pb, gb))
     lam0 = rng.standard_normal((batch, N * nx)).astype(np.float32)
-    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 0, g._lib.FLAG_TMEM)
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 0, fl)
     assert np.array_equal(lam, lam0) and (it == 0).all() and (ex == 1).all()
-    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 3, g._lib.FLAG_TMEM)
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 3, fl)
     assert (it == 3).all() and (ex == 1).all() and np.isfinite(lam).all()
-    lam_w, it_w, ex_w = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, g._lib.FLAG_TMEM)
+    lam_w, it_w, ex_w = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, fl)
     lam_r, it_r, ex_r = _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, g._lib.FLAG_NO_TMEM)
-    assert not ex_w.any() and np.array_equal(it_w, it_r) and np.array_equal(lam_w.view(np.uint32), lam_r.view(np.uint32))
+    assert not ex_w.any() and np.abs(it_w.astype(int) - it_r.astype(int)).max() <= 1
+    if arm == "r2":
+        assert np.array_equal(it_w, it_r) and np.array_equal(lam_w.view(np.uint32), lam_r.view(np.uint32))
     for s in range(4):
         check_against_oracle(S[s], P[s], gam[s], lam0[s], nx, N, 1e-6, 1000, lam_w[s], int(it_w[s]), bool(ex_w[s]))
 
@@ -652,3 +730,35 @@ def test_tmem_kernel_selection_and_refusals():
     assert np.array_equal(it_u, it_a) and np.array_equal(lam_u, lam_a)
     with pytest.raises(g.GbdpcgError):
         _batched(nx, N, batch, d_S, d_P, d_g, lam0, 1e-6, 1000, g._lib.FLAG_TMEM)
+
+
+@pytest.mark.parametrize("arm", ["r4", "r2"])
+@pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 32, 2048), (16, 8, 32, 1500), (12, 4, 40, 1111)])
+def test_tmem_kernels_are_deterministic_under_concurrent_launches(nx, nu, N, batch, arm):
+    """The -m gpu form of scripts/stress_tmem.py (compute-sanitizer is closed on this pool, so repeat-and-compare is the race
+    evidence): the same batch 50 times, every second time with a SECOND launch of the same kernel on another stream so that CTAs
+    of two launches share SMs and the 512 tensor-memory columns (tcgen05.alloc of the late CTAs blocks until columns are free).
+    Every lambda and iteration count must be bit-identical to the first run, in both launches."""
+    torch = _torch()
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(16), "stair", np.float32)
+    r = (batch + 15) // 16
+    d_S, d_P, d_g = (torch.from_numpy(np.tile(a, (r, 1))[:batch].copy()).cuda() for a in (S, P, gam))
+    cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0, flags=TMEM_ARMS[arm]())
+    s2 = torch.cuda.Stream()
+    ref = None
+    for i in range(50):
+        d_l = torch.zeros(batch, N * nx, dtype=torch.float32, device="cuda")
+        d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+        d_l2 = torch.zeros(batch, N * nx, dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+        g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, None)
+        if i % 2:
+            with torch.cuda.stream(s2):
+                g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l2, cfg, None, None, stream=s2)
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = (d_l.clone(), d_it.clone())
+            assert int(d_it.min().item()) > 5
+        else:
+            assert torch.equal(d_l, ref[0]) and torch.equal(d_it, ref[1]), f"run {i} differs"
+            assert i % 2 == 0 or torch.equal(d_l2, ref[0]), f"run {i}: the concurrent launch differs"
