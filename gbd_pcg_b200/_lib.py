@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("GBDPCG_LIB") or os.path.join(_HERE, "libgbdpcg.so")
 
 OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM = 0, -1, -2, -3, -4
 FLAG_FORCE_GENERIC, FLAG_PINV_SMEM, FLAG_PINV_REG = 0x1, 0x2, 0x4
-FLAG_TEXTBOOK, FLAG_FUSED, FLAG_LEGACY_ROWS, FLAG_NO_TMA, FLAG_SLAB_LAYOUT = 0x8, 0x10, 0x20, 0x40, 0x80
+FLAG_TEXTBOOK, FLAG_FUSED, FLAG_LEGACY_ROWS, FLAG_NO_TMA = 0x8, 0x10, 0x20, 0x40
 FLAG_BUILD_JACOBI, FLAG_BUILD_STAIR = 0x100, 0x200
 FLAG_TMEM, FLAG_NO_TMEM, FLAG_TMEM_R2 = 0x400, 0x800, 0x1000
 PINV_IDENTITY, PINV_JACOBI, PINV_STAIR = 0, 1, 2
@@ -65,7 +65,7 @@ for _s in ("f32", "f64"):
     SIGNATURES[f"gbdpcg_build_pinv_host_{_s}"] = (C.c_int, [_VP] * 3 + [_U32, _U32, _U32, C.c_int])
     SIGNATURES[f"gbdpcg_schur_form_dev_{_s}"] = (C.c_int, [_VP] * 8 + [_U32] * 4 + [_VP] * 5)
     SIGNATURES[f"gbdpcg_schur_recover_dev_{_s}"] = (C.c_int, [_VP] * 8 + [_U32] * 4 + [_VP] * 3)
-    SIGNATURES[f"gbdpcg_pack_csr_dev_{_s}"] = (C.c_int, [_VP] * 4 + [_U32, _U32, _U32, _VP, _VP, _VP])
+    SIGNATURES[f"gbdpcg_pack_csr_dev_{_s}"] = (C.c_int, [_VP] * 4 + [_U32, _U32, _U32, _U32, _VP, _VP, _VP])
     SIGNATURES[f"gbdpcg_solve_csr_host_{_s}"] = (C.c_int, [_VP] * 4 + [_U32] + [_VP] * 3 + [_U32, _VP, _VP, _U32, _U32, _CFG,
                                                             C.POINTER(_U32), C.POINTER(_I32)])
 

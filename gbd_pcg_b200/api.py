@@ -233,12 +233,15 @@ def _solve_csr(h_S, h_Pinv, h_gamma, h_lambda, stateSize, knotPoints, config=Non
     return (it.value, bool(ex.value)) if return_flag else it.value
 
 
-def pack_csr_dev(d_row_ptr, d_col_ind, d_val, rows, state_size, knot_points, d_out, d_status=None, stream=None):
+def pack_csr_dev(d_row_ptr, d_col_ind, d_val, rows, state_size, knot_points, d_out, d_status=None, stream=None, nnz=None):
     """Device CSR -> compressed block-tridiagonal layout (asynchronous).  ``d_status`` (int32[1]) gets bit 0 set when an
-    entry lies outside the band."""
+    entry lies outside the band, bit 1 when row_ptr decreases or runs past ``nnz`` (default: the length of ``d_val``);
+    such rows are clamped, never read out of bounds."""
     suf = _torch_dtype_suffix(d_val)
+    if nnz is None:
+        nnz = int(d_val.numel())
     f = getattr(_lib.lib(), f"gbdpcg_pack_csr_dev_{suf}")
-    _lib.check(f(None, _dev_ptr(d_row_ptr, "d_row_ptr"), _dev_ptr(d_col_ind, "d_col_ind"), _dev_ptr(d_val, "d_val"), int(rows),
+    _lib.check(f(None, _dev_ptr(d_row_ptr, "d_row_ptr"), _dev_ptr(d_col_ind, "d_col_ind"), _dev_ptr(d_val, "d_val"), int(nnz), int(rows),
                  int(state_size), int(knot_points), _dev_ptr(d_out, "d_out"), _dev_ptr(d_status, "d_status", True), _stream_ptr(stream)))
 
 

@@ -15,7 +15,6 @@
 #include "gbdpcg.h"
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
-#include "pcg_slab.cuh"
 #include "pcg_tmem4.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_rows.cuh"
@@ -145,9 +144,7 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
             const int bpc = ((int)N + cl - 1) / cl;
             for (int i = 0; i < cnt; i++) {
                 const FusedVariant *v = &tab[i];
-                if (v->slab && !(cfg.flags & GBDPCG_FLAG_SLAB_LAYOUT)) continue;
-                if (v->slab && v->pmode == P_REG && v->maxt <= 32) continue;    // slab P_REG not buildable for this nx
-                const int threads = v->slab ? slab_threads((int)nx, bpc) : round_up(bpc * ((int)nx / v->rpt), 32);
+                const int threads = round_up(bpc * ((int)nx / v->rpt), 32);
                 if (v->clustered != (cl > 1) || v->pmode != pm_opts[ip] || threads > v->maxt) continue;
                 const size_t smem = make_fused_plan<T>((int)nx, v->nxp, bpc, v->pmode, v->pmode == P_REG ? 2 : 1).total;
                 if (smem > kMaxDynSmem) continue;
@@ -159,7 +156,7 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
                 // 88 -> 55; profiles/clusters_r1e.txt) -- as long as every system of the batch still gets its own cluster in
                 // one wave and a CTA keeps at least two warps.  One CTA with Phi^-1 in registers stays one CTA (C2: 26.7 us
                 // against 37), and large batches keep the smallest cluster: fewest SMs per system.
-                if (cl > 1 && !cfg.cluster && !v->slab && v->fused) {
+                if (cl > 1 && !cfg.cluster && v->fused) {
                     const unsigned long long sms = (unsigned long long)device_sms();
                     for (int big = 16; big > cl; big >>= 1) {
                         if ((unsigned long long)batch * big > sms) continue;
@@ -207,19 +204,21 @@ static size_t tmem_smem_request(size_t need, int per_sm)
 static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
 {
     if (!has_p || (nx & 1u) || nx > 16 || N < 2 || cfg.cluster > 1) return false;
-    if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA)) return false;
+    if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_NO_TMA)) return false;
     const char *name = nullptr;
     if (!(cfg.flags & GBDPCG_FLAG_TMEM_R2)) {
-        int variant = 0, cols = 0;
+        const int threads4 = round_up((int)(N * ((nx + 3) / 4)), 32);
+        int variant = threads4 <= 64 ? 10 : 0, cols = 0;                                        // <= 2 warps: the <= 128-column variant, four CTAs per SM
         if (const char *e = getenv("GBDPCG_TMEM4_VARIANT")) variant = atoi(e);                  // tuning knob (A/B runs)
         const void *fn4 = tmem4_kernel_f32((int)nx, variant, &name, &cols);
-        const int threads4 = round_up((int)(N * ((nx + 3) / 4)), 32);
         if (fn4 && threads4 <= kTmem4MaxThreads) {
             int per_sm = 512 / cols;
             const int by_regs = 65536 / (256 * threads4);                                      // __launch_bounds__(128, 2): up to 255 registers
             if (by_regs < per_sm) per_sm = by_regs;
             const size_t need = make_tmem4_plan((int)nx, Geo<float>::nxp((int)nx), (int)N).total;
-            if ((size_t)per_sm * (need + 1024) <= 233472) {
+            // worth it with at least 8 warps on an SM (nx=12,N=20 at 2 x 2 warps: 0.48 ms against 0.40 for the two-row kernel; profiles/tmem4_r2a.txt)
+            const bool enough_warps = per_sm * threads4 >= 256 || (cfg.flags & GBDPCG_FLAG_TMEM) || getenv("GBDPCG_TMEM4_VARIANT");
+            if (enough_warps && (size_t)per_sm * (need + 1024) <= 233472) {
                 out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->tmem_per_sm = per_sm; out->v = nullptr;
                 out->cluster = 1; out->bpc = (int)N; out->threads = threads4; out->nbuf = 1; out->pmode = P_REG;
                 out->smem = tmem_smem_request(need, per_sm); out->fn = fn4; out->name = name; out->rpt = 4; out->fused = 1;
@@ -257,7 +256,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     // 1.43 -> 1.00; nx=10,N=17: 0.42 -> 0.35; profiles/tmem_r1g.txt).
     if constexpr (!f64) {
         const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
-                                  GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_SLAB_LAYOUT | GBDPCG_FLAG_NO_TMA;
+                                  GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_NO_TMA;
         // (two-row kernel: systems of <= 64 threads lose, the register-row kernel already fits four of them on an SM -- nx=8,N=16: 0.19 vs 0.21 ms)
         Plan tp;
         if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_tmem(nx, N, has_p, cfg, &tp) &&
@@ -414,13 +413,13 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
     KernelArgs<T> a;
     a.S = S; a.Pinv = P; a.gamma = gamma; a.lambda = lambda; a.iters = d_iters; a.exits = d_exits;
     a.mat_stride = 3ull * N * nx * nx; a.vec_stride = (unsigned long long)N * nx;
-    a.N = N; a.batch = batch; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg.max_iter; a.two_buffers = (p.nbuf == 2);
+    a.N = N; a.batch = batch; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg.max_iter; a.two_buffers = (p.nbuf == 2); a.use_tma = 0;
     if (p.fused_kernel) {
-        // field reused as the TMA switch: bulk copies need 16-byte aligned sources (strides are multiples of 16 for even nx)
+        // bulk copies (TMA) need 16-byte aligned sources (strides are multiples of 16 for even nx)
         // (odd nx: a block-row is not a multiple of 16 bytes, so a CTA's share of the matrix is not bulk-copyable)
         const bool aligned = ((uintptr_t)S % 16 == 0) && (!P || (uintptr_t)P % 16 == 0) && ((a.mat_stride * sizeof(T)) % 16 == 0) &&
                              ((3ull * nx * nx * sizeof(T)) % 16 == 0);
-        a.two_buffers = (aligned && p.pmode != P_SMEM && !(cfg.flags & GBDPCG_FLAG_NO_TMA)) ? 1u : 0u;
+        a.use_tma = (aligned && p.pmode != P_SMEM && !(cfg.flags & GBDPCG_FLAG_NO_TMA)) ? 1u : 0u;
     }
     a.tol = (T)cfg.exit_tol;
 
@@ -559,6 +558,14 @@ static int get_ws(gbdpcg_workspace *user, gbdpcg_workspace **out)
     return GBDPCG_OK;
 }
 
+// Blocking host entry points: a failure after the first enqueue must not return while copies into the caller's arrays or kernels on
+// the workspace buffers are still in flight.  Synchronises the stream on scope exit unless disarmed after the regular synchronize.
+struct StreamDrain {
+    cudaStream_t st;
+    bool armed = true;
+    ~StreamDrain() { if (armed) { cudaStreamSynchronize(st); cudaGetLastError(); } }
+};
+
 // ------------------------------------------------------------------------------------------------
 // typed implementations
 // ------------------------------------------------------------------------------------------------
@@ -638,6 +645,7 @@ static int solve_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const
     if ((rc = ws_reserve(w, 2, vb))) return rc;
     if ((rc = ws_reserve(w, 3, vb))) return rc;
     cudaStream_t st = w->streams[0];
+    StreamDrain drain{st};
     CK(cudaMemcpyAsync(w->dbuf[0], hS, mb, cudaMemcpyHostToDevice, st));
     if (bk >= 0) { if ((rc = build_pinv_dev<T>((const T *)w->dbuf[0], (T *)w->dbuf[1], nx, N, 1, bk, st))) return rc; }
     else if (has_p) CK(cudaMemcpyAsync(w->dbuf[1], hP, mb, cudaMemcpyHostToDevice, st));
@@ -650,6 +658,7 @@ static int solve_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const
     if (rc) return rc;
     CK(cudaMemcpyAsync(hl, w->dbuf[3], vb, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    drain.armed = false;
     if (iters) *iters = *(volatile uint32_t *)w->h_iters;
     if (max_iter_exit) *max_iter_exit = *(volatile uint8_t *)w->h_exit;
     return GBDPCG_OK;
@@ -693,6 +702,12 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     if (chunk > batch) chunk = batch;
 
     T *dS = (T *)w->dbuf[0], *dP = (T *)w->dbuf[1], *dg = (T *)w->dbuf[2], *dl = (T *)w->dbuf[3];
+    // A failure after the first enqueue must not return while earlier chunks are still in flight (D2H copies into the caller's
+    // lambda, kernels on the workspace buffers): drain both streams first, ignoring what the drain itself reports.
+    struct Drain {
+        gbdpcg_workspace *w; bool armed = true;
+        ~Drain() { if (armed) { cudaStreamSynchronize(w->streams[0]); cudaStreamSynchronize(w->streams[1]); cudaGetLastError(); } }
+    } drain{w};
     int ci = 0;
     for (size_t o = 0; o < batch; o += chunk, ci++) {
         const size_t n = (batch - o < chunk) ? batch - o : chunk;
@@ -711,6 +726,7 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     }
     CK(cudaStreamSynchronize(w->streams[0]));
     CK(cudaStreamSynchronize(w->streams[1]));
+    drain.armed = false;
     if (h_iters) memcpy(h_iters, w->p_iters, sizeof(uint32_t) * batch);
     if (h_exits) memcpy(h_exits, w->p_exits, batch);
     return GBDPCG_OK;
@@ -730,10 +746,12 @@ static int build_pinv_host(gbdpcg_workspace *user_ws, const T *hS, T *hP, uint32
     if ((rc = ws_reserve(w, 0, mb))) return rc;
     if ((rc = ws_reserve(w, 1, mb))) return rc;
     cudaStream_t st = w->streams[0];
+    StreamDrain drain{st};
     CK(cudaMemcpyAsync(w->dbuf[0], hS, mb, cudaMemcpyHostToDevice, st));
     if ((rc = build_pinv_dev<T>((const T *)w->dbuf[0], (T *)w->dbuf[1], nx, N, batch, kind, st))) return rc;
     CK(cudaMemcpyAsync(hP, w->dbuf[1], mb, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    drain.armed = false;
     return GBDPCG_OK;
 }
 
@@ -749,9 +767,7 @@ static int schur_form_dev(const T *Q, const T *R, const T *A, const T *B, const 
     SchurArgs a;
     a.Q = Q; a.R = R; a.A = A; a.B = B; a.q = q; a.r = r; a.c = c; a.S = S; a.gamma = gamma; a.Qinv = Qinv; a.Rinv = Rinv;
     a.nx = nx; a.nu = nu; a.N = N; a.batch = batch;
-    int sms = 148, dev = 0;
-    CK(cudaGetDevice(&dev));
-    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int sms = device_sms();
     // compiled state sizes with nu <= nx: chunked, lane-per-columns kernel
     const void *fn_nx = nullptr;
     if (nu <= nx) {
@@ -796,7 +812,8 @@ static int schur_form_dev(const T *Q, const T *R, const T *A, const T *B, const 
     int rc = prepare_fn(fn, false);
     if (rc) return rc;
     const unsigned long long items = (unsigned long long)batch * N;
-    const uint32_t grid = (uint32_t)(items < 148ull * 16 ? items : 148ull * 16);
+    const unsigned long long cap16 = (unsigned long long)sms * 16;
+    const uint32_t grid = (uint32_t)(items < cap16 ? items : cap16);
     schur_form_kernel<T><<<grid, 128, smem, st>>>(a);
     CK(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -811,12 +828,13 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
     if (nx == 0 || nu == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0, nu > 0 and N >= 2");
     if (batch == 0) return GBDPCG_OK;
     const unsigned long long items = (unsigned long long)batch * N;
+    const unsigned long long sms = (unsigned long long)device_sms();
     if (nx <= 32 && nu <= 32) {
         const unsigned long long ctas = (items + 7) / 8;                       // one warp per (system, knot)
-        const uint32_t grid = (uint32_t)(ctas < 148ull * 8 ? ctas : 148ull * 8);
+        const uint32_t grid = (uint32_t)(ctas < sms * 8 ? ctas : sms * 8);
         schur_recover_warp_kernel<T><<<grid, 256, 0, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
     } else {
-        const uint32_t grid = (uint32_t)(items < 148ull * 32 ? items : 148ull * 32);
+        const uint32_t grid = (uint32_t)(items < sms * 32 ? items : sms * 32);
         schur_recover_kernel<T><<<grid, 64, (nx + nu) * sizeof(T) + 16, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
     }
     CK(cudaGetLastError());
@@ -826,17 +844,18 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
 
 // ---- CSR front end (reference include/interface.cuh:8-20 is a stub) ----
 template <typename T>
-static int pack_csr_dev(const uint32_t *row_ptr, const uint32_t *col_ind, const T *val, uint32_t rows, uint32_t nx, uint32_t N,
+static int pack_csr_dev(const uint32_t *row_ptr, const uint32_t *col_ind, const T *val, uint32_t nnz, uint32_t rows, uint32_t nx, uint32_t N,
                         T *out, int32_t *d_status, cudaStream_t st)
 {
-    if (!row_ptr || !col_ind || !val || !out) return fail(GBDPCG_ERR_INVALID, "CSR arrays and the output must not be NULL");
+    if (!row_ptr || !out || (nnz && (!col_ind || !val))) return fail(GBDPCG_ERR_INVALID, "CSR arrays and the output must not be NULL");
     if (nx == 0 || N < 2) return fail(GBDPCG_ERR_INVALID, "need nx > 0 and N >= 2");
     if ((uint64_t)rows != (uint64_t)nx * N) return fail(GBDPCG_ERR_INVALID, "CSR matrix has %u rows, expected stateSize*knotPoints = %llu", rows,
                                                         (unsigned long long)nx * N);
     CK(cudaMemsetAsync(out, 0, sizeof(T) * 3 * (size_t)N * nx * nx, st));
     if (d_status) CK(cudaMemsetAsync(d_status, 0, sizeof(int32_t), st));
-    const uint32_t blocks = (rows + 7) / 8 < 1184 ? (rows + 7) / 8 : 1184;       // one warp per row, at most 8 CTAs per SM
-    csr_pack_kernel<T><<<blocks, 256, 0, st>>>(row_ptr, col_ind, val, rows, nx, N, out, d_status);
+    const uint32_t cap8 = (uint32_t)device_sms() * 8;
+    const uint32_t blocks = (rows + 7) / 8 < cap8 ? (rows + 7) / 8 : cap8;       // one warp per row, at most 8 CTAs per SM
+    csr_pack_kernel<T><<<blocks, 256, 0, st>>>(row_ptr, col_ind, val, nnz, rows, nx, N, out, d_status);
     CK(cudaGetLastError());
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return GBDPCG_OK;
@@ -851,6 +870,21 @@ static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const
     int rc = check_args(S.val, hg, hl, nx, N, cfg);
     if (rc) return rc;
     if (!S.row_ptr || !S.col_ind) return fail(GBDPCG_ERR_INVALID, "S.row_ptr and S.col_ind must not be NULL");
+    // The CSR arrays are host pointers: hold row_ptr to the CSR contract BEFORE anything is uploaded, so a malformed csr_t can
+    // neither over-read the device staging buffers (sized from nnz) nor fault the context.
+    {
+        const uint32_t nrows = nx * N;
+        auto check_csr = [&](const HostCsr &M, const char *name) -> int {
+            if (M.row_ptr[0] != 0) return fail(GBDPCG_ERR_INVALID, "%s.row_ptr[0] must be 0 (is %u)", name, M.row_ptr[0]);
+            for (uint32_t i = 0; i < nrows; i++)
+                if (M.row_ptr[i + 1] < M.row_ptr[i]) return fail(GBDPCG_ERR_INVALID, "%s.row_ptr decreases at row %u", name, i);
+            if (M.row_ptr[nrows] > M.nnz)
+                return fail(GBDPCG_ERR_INVALID, "%s.row_ptr[rows] = %u exceeds nnz = %u", name, M.row_ptr[nrows], M.nnz);
+            return GBDPCG_OK;
+        };
+        if ((rc = check_csr(S, "S"))) return rc;
+        if (P.val && P.row_ptr && P.col_ind && cfg->empty_pinv == 0 && build_kind(cfg) < 0 && (rc = check_csr(P, "Pinv"))) return rc;
+    }
     gbdpcg_workspace *w;
     if ((rc = get_ws(user_ws, &w))) return rc;
     std::lock_guard<std::mutex> lk(w->mu);
@@ -869,6 +903,7 @@ static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const
     if ((rc = ws_reserve(w, 6, sizeof(T) * (size_t)(max_nnz ? max_nnz : 1)))) return rc;
     if ((rc = ws_reserve(w, 7, 2 * sizeof(int32_t)))) return rc;
     cudaStream_t st = w->streams[0];
+    StreamDrain drain{st};
     int32_t *d_status = (int32_t *)w->dbuf[7];
     auto upload_and_pack = [&](const HostCsr &M, T *dst, int32_t *stat) -> int {
         CK(cudaMemcpyAsync(w->dbuf[4], M.row_ptr, sizeof(uint32_t) * ((size_t)rows + 1), cudaMemcpyHostToDevice, st));
@@ -876,7 +911,7 @@ static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const
             CK(cudaMemcpyAsync(w->dbuf[5], M.col_ind, sizeof(uint32_t) * (size_t)M.nnz, cudaMemcpyHostToDevice, st));
             CK(cudaMemcpyAsync(w->dbuf[6], M.val, sizeof(T) * (size_t)M.nnz, cudaMemcpyHostToDevice, st));
         }
-        return pack_csr_dev<T>((const uint32_t *)w->dbuf[4], (const uint32_t *)w->dbuf[5], (const T *)w->dbuf[6], rows, nx, N, dst, stat, st);
+        return pack_csr_dev<T>((const uint32_t *)w->dbuf[4], (const uint32_t *)w->dbuf[5], (const T *)w->dbuf[6], M.nnz, rows, nx, N, dst, stat, st);
     };
     if ((rc = upload_and_pack(S, (T *)w->dbuf[0], d_status))) return rc;
     if (csr_p) { if ((rc = upload_and_pack(P, (T *)w->dbuf[1], d_status + 1))) return rc; }
@@ -888,7 +923,8 @@ static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const
     CK(cudaMemcpyAsync(w->dbuf[3], hl, vb, cudaMemcpyHostToDevice, st));
     CK(cudaStreamSynchronize(st));
     if (h_status[0] || h_status[1])
-        return fail(GBDPCG_ERR_INVALID, "%s has entries outside the block-tridiagonal band of block size %u", h_status[0] ? "S" : "Pinv", nx);
+        return fail(GBDPCG_ERR_INVALID, "%s has entries outside the block-tridiagonal band of block size %u (or a malformed row_ptr)",
+                    h_status[0] ? "S" : "Pinv", nx);
     gbdpcg_config c1 = *cfg;
     c1.empty_pinv = has_p ? 0 : 1;
     rc = solve_batched_dev<T>((const T *)w->dbuf[0], has_p ? (const T *)w->dbuf[1] : nullptr, (const T *)w->dbuf[2], (T *)w->dbuf[3],
@@ -896,6 +932,7 @@ static int solve_csr_host(gbdpcg_workspace *user_ws, HostCsr S, HostCsr P, const
     if (rc) return rc;
     CK(cudaMemcpyAsync(hl, w->dbuf[3], vb, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    drain.armed = false;
     if (iters) *iters = *(volatile uint32_t *)w->h_iters;
     if (max_iter_exit) *max_iter_exit = *(volatile uint8_t *)w->h_exit;
     return GBDPCG_OK;
@@ -994,9 +1031,9 @@ void gbdpcg_workspace_destroy(gbdpcg_workspace *ws)
                                        const T *r, const T *lambda, uint32_t nx, uint32_t nu, uint32_t N, uint32_t batch, T *x,     \
                                        T *u, void *stream)                                                                          \
     { return schur_recover_dev<T>(Qinv, Rinv, A, B, q, r, lambda, nx, nu, N, batch, x, u, (cudaStream_t)stream); }                  \
-    int gbdpcg_pack_csr_dev_##SUF(gbdpcg_workspace *, const uint32_t *rp, const uint32_t *ci, const T *v, uint32_t rows,           \
-                                  uint32_t nx, uint32_t N, T *out, int32_t *d_status, void *stream)                                 \
-    { return pack_csr_dev<T>(rp, ci, v, rows, nx, N, out, d_status, (cudaStream_t)stream); }                                        \
+    int gbdpcg_pack_csr_dev_##SUF(gbdpcg_workspace *, const uint32_t *rp, const uint32_t *ci, const T *v, uint32_t nnz,            \
+                                  uint32_t rows, uint32_t nx, uint32_t N, T *out, int32_t *d_status, void *stream)                  \
+    { return pack_csr_dev<T>(rp, ci, v, nnz, rows, nx, N, out, d_status, (cudaStream_t)stream); }                                   \
     int gbdpcg_solve_csr_host_##SUF(gbdpcg_workspace *ws, const uint32_t *s_rp, const uint32_t *s_ci, const T *s_v, uint32_t s_nnz, \
                                     const uint32_t *p_rp, const uint32_t *p_ci, const T *p_v, uint32_t p_nnz, const T *g, T *l,     \
                                     uint32_t nx, uint32_t N, const gbdpcg_config *cfg, uint32_t *iters, int32_t *mie)               \

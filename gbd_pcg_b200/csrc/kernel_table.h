@@ -19,7 +19,7 @@ struct RowsVariant {
 
 // State sizes with a specialised kernel.  Keep in sync with NX_LIST in csrc/Makefile.
 #define GBDPCG_FOR_EACH_NX(X) X(2) X(4) X(6) X(8) X(10) X(12) X(14) X(16)
-// State sizes that get the fused solver kernel only, in its default single-reduction recurrence (no column-slab or
+// State sizes that get the fused solver kernel only, in its default single-reduction recurrence (no
 // first-generation variants, and the preconditioner builder / Schur kernels use their run-time-nx form): odd sizes
 // run one row per thread, sizes above 16 keep Phi^-1 in shared memory (fp64: up to 25, above that a row of S alone
 // overflows the register file and the table comes back empty).  Keep in sync with NX_EXTRA in the Makefile.
@@ -37,7 +37,6 @@ struct FusedVariant {
     int nx;
     int is_f64;
     int rpt;         // rows per thread
-    int slab;        // 1: column-slab layout (pcg_slab.cuh), 0: row layout (pcg_fused.cuh)
     int clustered;
     int pmode;
     int fused;       // 1: single-reduction (Chronopoulos-Gear) order, 0: the reference's two-reduction order

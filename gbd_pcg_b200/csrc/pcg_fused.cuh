@@ -419,7 +419,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int N = (int)a.N, bpc = (int)a.bpc;
-    const bool use_tma = a.two_buffers != 0;                                    // host decided: sources 16-byte aligned (field reused as the TMA switch)
+    const bool use_tma = a.use_tma != 0;                                        // host decided: sources 16-byte aligned
     constexpr int nstage = (PMODE == P_REG) ? 2 : 1;                            // staging holds S, and Phi^-1 beside it when both go to registers
     const FusedPlan plan = make_fused_plan<T>(NX, NXP, bpc, PMODE, nstage);
     T *red = reinterpret_cast<T *>(smem_raw + plan.red_off);

@@ -1,8 +1,7 @@
 // pcg_fused_inst.cu -- instantiates the fused kernel (pcg_fused.cuh) for one (dtype, nx, recurrence); compiled
-// once per triple with  -DINST_NX=<nx> -DINST_F64=<0|1> -DINST_FUSED=<0|1> [-DINST_NO_SLAB]   (see csrc/Makefile)
+// once per triple with  -DINST_NX=<nx> -DINST_F64=<0|1> -DINST_FUSED=<0|1>   (see csrc/Makefile)
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
-#include "pcg_slab.cuh"
 
 #if !defined(INST_NX) || !defined(INST_F64) || !defined(INST_FUSED)
 #error "compile with -DINST_NX=<state size> -DINST_F64=<0|1> -DINST_FUSED=<0|1>"
@@ -58,32 +57,11 @@ constexpr int MAXT_2K = MAXT_2 > 0 ? MAXT_2 : 32;
 constexpr bool FUSED = INST_FUSED != 0;
 
 #define VARIANT(CL, PM, MT)                                                                                   \
-    {NX, INST_F64, RPT, 0, CL, PM, INST_FUSED, MT, Geo<InstT>::nxp(NX),                                         \
+    {NX, INST_F64, RPT, CL, PM, INST_FUSED, MT, Geo<InstT>::nxp(NX),                                            \
      (const void *)pcg_fused_kernel<InstT, NX, RPT, PM, FUSED, (CL != 0), MT>,                                 \
      "pcg_fused<" INST_DT ",nx=" STR(INST_NX) ",R=" STR(INST_RPT) "," #CL "," #PM "," STR(INST_FUSED) ">"}
 
-// column-slab layout (fp32 only): 6*nx matrix entries per thread and matrix, nx accumulators
-constexpr int slab_maxt_for(int nx, int nmat_reg)
-{
-    int r = (6 * nx * nmat_reg + nx + 56 + 7) / 8 * 8;
-    if (r > 255) return 0;
-    int t = 128 * (512 / r);
-    return t > 1024 ? 1024 : t;
-}
-constexpr int SMAXT_1 = slab_maxt_for(NX, 1) > 0 ? slab_maxt_for(NX, 1) : 32;
-constexpr int SMAXT_2 = slab_maxt_for(NX, 2);
-constexpr int SMAXT_2K = SMAXT_2 > 32 ? SMAXT_2 : 32;
-#define SLAB_VARIANT(CL, PM, MT)                                                                              \
-    {NX, INST_F64, 2, 1, CL, PM, INST_FUSED, MT, NX,                                                           \
-     (const void *)pcg_slab_kernel<InstT, NX, PM, FUSED, (CL != 0), MT>,                                       \
-     "pcg_slab<" INST_DT ",nx=" STR(INST_NX) "," #CL "," #PM "," STR(INST_FUSED) ">"}
-
 static const FusedVariant g_table[] = {
-#if !INST_F64 && !defined(INST_NO_SLAB)
-    // selected only with GBDPCG_FLAG_SLAB_LAYOUT
-    SLAB_VARIANT(0, P_NONE, SMAXT_1), SLAB_VARIANT(1, P_NONE, SMAXT_1),
-    SLAB_VARIANT(0, P_REG, SMAXT_2K), SLAB_VARIANT(1, P_REG, SMAXT_2K),
-#endif
     VARIANT(0, P_NONE, MAXT_1), VARIANT(1, P_NONE, MAXT_1),
     VARIANT(0, P_SMEM, MAXT_1), VARIANT(1, P_SMEM, MAXT_1),
     VARIANT(0, P_REG, MAXT_2K), VARIANT(1, P_REG, MAXT_2K),

@@ -43,7 +43,8 @@ struct KernelArgs {
     uint32_t batch;
     uint32_t bpc;                  // block-rows per CTA
     uint32_t max_iter;
-    uint32_t two_buffers;          // 1: S and Phi^-1 staged side by side; 0: through one buffer in turn
+    uint32_t two_buffers;          // first-generation kernel (pcg_rows): 1 = S and Phi^-1 staged side by side, 0 = through one buffer in turn
+    uint32_t use_tma;              // pcg_fused: 1 = matrices arrive by cp.async.bulk (16-byte aligned sources), 0 = cooperative loads
     T tol;
 };
 

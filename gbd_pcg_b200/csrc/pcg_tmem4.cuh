@@ -29,6 +29,9 @@
 
 #include "pcg_tmem.cuh"
 
+#ifndef TMEM4_SCALAR_FMA
+#define TMEM4_SCALAR_FMA 0    // 1: scalar FFMA instead of the packed FFMA2 (A/B: a packed multiply-add reads three 64-bit register operands)
+#endif
 #ifndef TMEM4_L2_PREFETCH
 #define TMEM4_L2_PREFETCH 1   // pull the next system's S into L2 behind the iterations (its bulk copy into the one staging buffer is exposed)
 #endif
@@ -171,15 +174,25 @@ __device__ __forceinline__ float4 t4_window_quad(const float *w)
         return make_float4(h.x, h.y, 0.f, 0.f);
     }
 }
+// acc += (m0, m1) * (x0, x1), packed (FFMA2) or as two scalar FFMAs
+__device__ __forceinline__ void t4_fma2(float2 &acc, float m0, float m1, float x0, float x1)
+{
+#if TMEM4_SCALAR_FMA
+    acc.x = fmaf(m0, x0, acc.x);
+    acc.y = fmaf(m1, x1, acc.y);
+#else
+    acc = __ffma2_rn(make_float2(m0, m1), make_float2(x0, x1), acc);
+#endif
+}
 template <class GEO, int NXP, int Q>
 __device__ __forceinline__ void t4_fma_reg(const float (&m)[4][4], const float *w, float2 (&acc)[4])
 {
     const float4 x = t4_window_quad<GEO, NXP, Q>(w);
 #pragma unroll
-    for (int row = 0; row < 4; row++) acc[row] = __ffma2_rn(make_float2(m[row][0], m[row][1]), make_float2(x.x, x.y), acc[row]);
+    for (int row = 0; row < 4; row++) t4_fma2(acc[row], m[row][0], m[row][1], x.x, x.y);
     if constexpr (GEO::qw(Q) == 4) {
 #pragma unroll
-        for (int row = 0; row < 4; row++) acc[row] = __ffma2_rn(make_float2(m[row][2], m[row][3]), make_float2(x.z, x.w), acc[row]);
+        for (int row = 0; row < 4; row++) t4_fma2(acc[row], m[row][2], m[row][3], x.z, x.w);
     }
 }
 template <class GEO, int NXP, int Q>
@@ -188,12 +201,10 @@ __device__ __forceinline__ void t4_fma_tm(const uint32_t (&u)[16], const float *
     constexpr int W = GEO::qw(Q);
     const float4 x = t4_window_quad<GEO, NXP, Q>(w);
 #pragma unroll
-    for (int row = 0; row < 4; row++)
-        acc[row] = __ffma2_rn(make_float2(__uint_as_float(u[row * W]), __uint_as_float(u[row * W + 1])), make_float2(x.x, x.y), acc[row]);
+    for (int row = 0; row < 4; row++) t4_fma2(acc[row], __uint_as_float(u[row * W]), __uint_as_float(u[row * W + 1]), x.x, x.y);
     if constexpr (W == 4) {
 #pragma unroll
-        for (int row = 0; row < 4; row++)
-            acc[row] = __ffma2_rn(make_float2(__uint_as_float(u[row * W + 2]), __uint_as_float(u[row * W + 3])), make_float2(x.z, x.w), acc[row]);
+        for (int row = 0; row < 4; row++) t4_fma2(acc[row], __uint_as_float(u[row * W + 2]), __uint_as_float(u[row * W + 3]), x.z, x.w);
     }
 }
 template <class GEO, bool IS_S, int K>

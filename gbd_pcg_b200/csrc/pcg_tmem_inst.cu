@@ -24,11 +24,13 @@ const void *tmem4_kernel_f32(int nx, int variant, const char **name, int *alloc_
         *alloc_cols = T4Geo<NX, SQT, PQR>::alloc_cols;                                      \
         return (const void *)pcg_tmem4_kernel<NX, SQT, PQR>;                                \
     }
-    V(8, 0, 0, 0)
-    V(10, 0, 0, 0)
-    V(12, 0, 0, 0) V(12, 1, 3, 3)
-    V(14, 0, 0, 0) V(14, 1, 4, 0) V(14, 2, 6, 6) V(14, 3, 3, 3) V(14, 4, 2, 0)
-    V(16, 0, 4, 0) V(16, 1, 6, 2)
+    // id 0: what the planner takes for systems of 3..4 warps; id 10: systems of <= 2 warps -- at most 128 tensor-memory columns,
+    // so that FOUR CTAs share an SM; the rest: alternatives kept for A/B runs (profiles/tmem4_r2*.txt)
+    V(8, 0, 0, 0) V(8, 10, 0, 0)
+    V(10, 0, 0, 0) V(10, 10, 0, 0)
+    V(12, 0, 3, 3) V(12, 1, 0, 0) V(12, 10, 0, 1)
+    V(14, 0, 2, 0) V(14, 1, 4, 0) V(14, 2, 6, 6) V(14, 3, 0, 0) V(14, 10, 0, 3)
+    V(16, 0, 6, 2) V(16, 1, 4, 0)
 #undef V
     *name = nullptr;
     *alloc_cols = 0;

@@ -66,8 +66,6 @@ typedef struct gbdpcg_config {
 #define GBDPCG_FLAG_FUSED 0x10u        /* single-reduction (Chronopoulos-Gear) form of the same recurrence
                                           (the default for both precisions)                                   */
 #define GBDPCG_FLAG_LEGACY_ROWS 0x20u  /* first-generation one-row-per-thread kernel (kept for A/B measurements) */
-#define GBDPCG_FLAG_SLAB_LAYOUT 0x80u  /* fp32: column-slab ownership of the matrix entries (pcg_slab.cuh); fewer shared-memory
-                                          bytes per mat-vec, more instructions -- measured slower on C2, kept for A/B */
 #define GBDPCG_FLAG_NO_TMA 0x40u       /* stage matrices with ordinary loads instead of cp.async.bulk           */
 /* Host entry points only: form Phi^-1 from S ON THE DEVICE (gbdpcg_build_pinv_*) instead of taking it from the caller;
  * the Pinv argument and empty_pinv are then ignored.  This is what makes the reference's own host signature
@@ -194,14 +192,17 @@ GBDPCG_API int gbdpcg_schur_recover_dev_f64(gbdpcg_workspace *ws, const double *
  *    (include/interface.cuh:8-20 prints "NOT IMPLEMENTED" and exits 12; csr_t<T>: include/types.cuh:7-15).
  *    _pack_csr_dev: device CSR (rows = nx*N, uint32 row_ptr[rows+1] / col_ind[nnz], T val[nnz]) -> compressed
  *      block-tridiagonal layout in d_out (zeroed by the call); duplicates are summed; an entry outside the band sets
- *      bit 0 of *d_status (device int32, may be NULL) and is dropped.  Asynchronous on `stream`.
+ *      bit 0 of *d_status (device int32, may be NULL) and is dropped; a row_ptr that decreases or runs
+ *      past `nnz` (the number of entries col_ind / val hold) sets bit 1 and is clamped -- the kernel never reads outside
+ *      col_ind[0..nnz) / val[0..nnz).  Asynchronous on `stream`.
  *    _solve_csr_host: blocking solve with S (and optionally Phi^-1) given as host CSR.  Phi^-1 is used when its arrays
  *      are non-NULL and cfg->empty_pinv == 0; GBDPCG_FLAG_BUILD_* forms it from S instead.  Returns
- *      GBDPCG_ERR_INVALID when an entry lies outside the block-tridiagonal band. */
+ *      GBDPCG_ERR_INVALID when an entry lies outside the block-tridiagonal band, and -- checked on the host before anything is
+ *      uploaded -- when row_ptr[0] != 0, row_ptr decreases, or row_ptr[rows] > nnz. */
 GBDPCG_API int gbdpcg_pack_csr_dev_f32(gbdpcg_workspace *ws, const uint32_t *d_row_ptr, const uint32_t *d_col_ind, const float *d_val,
-                                       uint32_t rows, uint32_t nx, uint32_t N, float *d_out, int32_t *d_status, void *stream);
+                                       uint32_t nnz, uint32_t rows, uint32_t nx, uint32_t N, float *d_out, int32_t *d_status, void *stream);
 GBDPCG_API int gbdpcg_pack_csr_dev_f64(gbdpcg_workspace *ws, const uint32_t *d_row_ptr, const uint32_t *d_col_ind, const double *d_val,
-                                       uint32_t rows, uint32_t nx, uint32_t N, double *d_out, int32_t *d_status, void *stream);
+                                       uint32_t nnz, uint32_t rows, uint32_t nx, uint32_t N, double *d_out, int32_t *d_status, void *stream);
 GBDPCG_API int gbdpcg_solve_csr_host_f32(gbdpcg_workspace *ws, const uint32_t *S_row_ptr, const uint32_t *S_col_ind, const float *S_val,
                                          uint32_t S_nnz, const uint32_t *P_row_ptr, const uint32_t *P_col_ind, const float *P_val,
                                          uint32_t P_nnz, const float *h_gamma, float *h_lambda, uint32_t nx, uint32_t N,

@@ -21,7 +21,7 @@ nseed = 16
 SHAPES = {"c5": [(14, 7, 32)],
           "all": [(14, 7, 32), (12, 4, 40), (16, 8, 30), (16, 8, 32), (8, 4, 60), (10, 5, 17), (12, 6, 20), (14, 7, 16), (8, 4, 16)],
           "small": [(10, 5, 17), (8, 4, 30), (12, 6, 20), (14, 7, 16), (16, 8, 16), (8, 4, 16)]}[which]
-NVAR = {8: 1, 10: 1, 12: 2, 14: 5, 16: 2}
+VARIANTS = {8: [0, 10], 10: [0, 10], 12: [0, 1, 10], 14: [0, 1, 2, 3, 10], 16: [0, 1]}
 
 
 def run(nx, N, d_S, d_P, d_g, flags, max_iter=1000, reps=11):
@@ -46,8 +46,10 @@ for (nx, nu, N) in SHAPES:
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", np.float32)
     d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // nseed, 1) for a in (S, P, gam))
     ora = [oracle.pcg(S[s], P[s], gam[s], np.zeros(N * nx, np.float32), nx, N, 1e-6, 1000) for s in range(nseed)]
-    arms = [("rows", F.FLAG_NO_TMEM, None), ("tmem_r2", F.FLAG_TMEM | F.FLAG_TMEM_R2, None)]
-    arms += [(f"tmem4_v{v}", F.FLAG_TMEM, v) for v in range(NVAR.get(nx, 0))]
+    arms = [("auto", 0, None), ("rows", F.FLAG_NO_TMEM, None), ("tmem_r2", F.FLAG_TMEM | F.FLAG_TMEM_R2, None)]
+    arms += [(f"tmem4_v{v}", F.FLAG_TMEM, v) for v in VARIANTS.get(nx, [])]
+    if os.environ.get("TMEM4_ARMS"):
+        arms = [a for a in arms if a[0] in os.environ["TMEM4_ARMS"].split(",")]
     for name, flags, var in arms:
         os.environ.pop("GBDPCG_TMEM4_VARIANT", None)
         if var is not None:

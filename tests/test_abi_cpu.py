@@ -134,3 +134,17 @@ def test_reference_style_example_compiles_against_the_new_headers(example, tmp_p
         env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(_lib.LIB_PATH) + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
         r = subprocess.run([str(exe)], env=env, capture_output=True, text=True)
         assert r.returncode != 0 and "GPUassert" in r.stderr       # loud failure, reference error convention
+
+
+def test_csr_row_ptr_is_validated_on_the_host_before_any_upload():
+    """A malformed csr_t (row_ptr[0] != 0, decreasing, or row_ptr[rows] > nnz) is refused with GBDPCG_ERR_INVALID by the host
+    check alone -- it answers the same way on a machine without a GPU, i.e. before any CUDA call."""
+    nx, N = 2, 4
+    rows = nx * N
+    col = np.array([0, 1, 2, 3], np.uint32)
+    val = np.array([1.0, 2.0, 3.0, 4.0])
+    for rp in ([0, 1, 2, 3, 4, 4, 4, 4, 1000], [0, 3, 1, 3, 4, 4, 4, 4, 4], [1, 1, 2, 3, 4, 4, 4, 4, 4]):
+        lam = np.zeros(rows)
+        with pytest.raises(g.GbdpcgError) as e:
+            g.solvePCG(g.csr_t(np.array(rp, np.uint32), col, val, rows, rows, 4), None, np.ones(rows), lam, nx, N, g.pcg_config())
+        assert e.value.status == _lib.ERR_INVALID and "row_ptr" in str(e.value)

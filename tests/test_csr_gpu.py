@@ -26,9 +26,35 @@ def pack_on_gpu(csr, nx, N, dtype):
     d_rp, d_ci, d_v = d(csr.row_ptr, np.uint32), d(csr.col_ind if csr.nnz else np.zeros(1), np.uint32), d(csr.val if csr.nnz else np.zeros(1), dtype)
     out = torch.full((3 * N * nx * nx,), float("nan"), dtype=d_v.dtype, device="cuda")
     status = torch.full((1,), -1, dtype=torch.int32, device="cuda")
-    g.pack_csr_dev(d_rp, d_ci, d_v, nx * N, nx, N, out, status)
+    g.pack_csr_dev(d_rp, d_ci, d_v, nx * N, nx, N, out, status, nnz=csr.nnz)
     torch.cuda.synchronize()
     return out.cpu().numpy(), int(status.item())
+
+
+def test_malformed_row_ptr_is_clamped_and_flagged():
+    """row_ptr that runs past nnz or decreases: the device packer must not read outside col_ind / val (status bit 1, entries
+    beyond nnz dropped); the host CSR solve refuses the matrix before anything is uploaded."""
+    nx, N = 2, 4
+    rows = nx * N
+    col = np.array([0, 1, 2, 3], np.uint32)
+    val = np.array([1.0, 2.0, 3.0, 4.0])
+    # (a) row_ptr[rows] = 1000 > nnz = 4
+    rp = np.array([0, 1, 2, 3, 4, 4, 4, 4, 1000], np.uint32)
+    out, status = pack_on_gpu(g.csr_t(rp, col, val, rows, rows, 4), nx, N, np.float64)
+    assert status & 2
+    want = np.zeros(3 * N * nx * nx)
+    for i in range(4):
+        want[(i // nx) * 3 * nx * nx + nx * nx + (i % nx) * nx + (i % nx)] = val[i]       # (i, i) on the diagonal blocks
+    assert np.array_equal(out, want)
+    # (b) decreasing row_ptr
+    rp2 = np.array([0, 3, 1, 3, 4, 4, 4, 4, 4], np.uint32)
+    _, status2 = pack_on_gpu(g.csr_t(rp2, col, val, rows, rows, 4), nx, N, np.float64)
+    assert status2 & 2
+    for bad in (rp, rp2, np.array([1, 1, 2, 3, 4, 4, 4, 4, 4], np.uint32)):
+        lam = np.zeros(rows)
+        with pytest.raises(g.GbdpcgError) as e:
+            g.solvePCG(g.csr_t(bad, col, val, rows, rows, 4), None, np.ones(rows), lam, nx, N, g.pcg_config())
+        assert e.value.status == _lib.ERR_INVALID and not lam.any()
 
 
 @pytest.mark.parametrize("precond", ["identity", "stair"])

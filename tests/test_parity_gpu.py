@@ -589,7 +589,7 @@ def test_python_mirror_workspace_handle():
 # ---------------------------------------------------------------------------------------------
 # kernel-selection flags: every recurrence / staging / generation variant solves the same systems
 # ---------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("flag", ["TEXTBOOK", "FUSED", "NO_TMA", "LEGACY_ROWS", "SLAB_LAYOUT"])
+@pytest.mark.parametrize("flag", ["TEXTBOOK", "FUSED", "NO_TMA", "LEGACY_ROWS"])
 @pytest.mark.parametrize("name,precond", [("C2", "stair"), ("C2", "identity"), ("C3", "stair"), ("C3", "identity"), ("C4", "jacobi")])
 def test_kernel_variant_flags(flag, name, precond):
     S, P, gam, nx, N, tol, max_iter = make_system(name, precond)
@@ -597,8 +597,6 @@ def test_kernel_variant_flags(flag, name, precond):
     flags = getattr(g._lib, "FLAG_" + flag)
     info = g.plan_query(nx, N, S.dtype, P is not None, g.pcg_config(flags=flags))
     assert ("pcg_rows" in info["kernel"]) == (flag == "LEGACY_ROWS")
-    if flag == "SLAB_LAYOUT" and S.dtype == np.float32 and info["pinv_mode"] != 2:
-        assert "pcg_slab" in info["kernel"]
     lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter, flags=flags)
     assert not ex
     check_against_oracle(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex)
@@ -707,11 +705,15 @@ def test_tmem_kernel_selection_and_refusals():
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms - 1)["kernel"]
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float64, True, cfg, batch=8192)["kernel"]
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, False, cfg, batch=8192)["kernel"]
-    # systems of <= 128 threads take 128 TMEM columns: four CTAs per SM, chosen once the batch fills them
-    assert "pcg_tmem" in g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms)["kernel"]
+    # the four-rows-per-thread kernel is the planner's choice where the system fits 128 such threads and an SM holds >= 8 warps of it
+    assert "pcg_tmem4" in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms)["kernel"]
+    assert "pcg_tmem4" in g.plan_query(12, 40, np.float32, True, cfg, batch=8192)["kernel"]
+    assert "pcg_tmem<" in g.plan_query(14, 32, np.float32, True, g.pcg_config(flags=g._lib.FLAG_TMEM_R2), batch=8192)["kernel"]
+    # systems of <= 2 warps take at most 128 tensor-memory columns: four CTAs per SM, chosen once the batch fills them
+    assert "pcg_tmem4" in g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms)["kernel"]
     assert g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms)["max_resident"] == 4 * sms
     assert "pcg_tmem" not in g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms - 1)["kernel"]
-    assert "pcg_tmem" not in g.plan_query(8, 16, np.float32, True, cfg, batch=8192)["kernel"]       # 64 threads: the register-row kernel fits four per SM itself
+    assert "pcg_tmem" not in g.plan_query(8, 16, np.float32, True, cfg, batch=8192)["kernel"]       # one warp per system: the register-row kernel wins
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, g.pcg_config(flags=g._lib.FLAG_NO_TMEM), batch=8192)["kernel"]
     for (nx, N, dt, has_p) in [(14, 32, np.float64, True), (14, 32, np.float32, False), (15, 20, np.float32, True), (18, 20, np.float32, True),
                                (14, 40, np.float32, True)]:
