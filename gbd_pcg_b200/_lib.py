@@ -16,7 +16,7 @@ OK, ERR_INVALID, ERR_CUDA, ERR_UNSUPPORTED, ERR_NOMEM = 0, -1, -2, -3, -4
 FLAG_FORCE_GENERIC, FLAG_PINV_SMEM, FLAG_PINV_REG = 0x1, 0x2, 0x4
 FLAG_TEXTBOOK, FLAG_FUSED, FLAG_LEGACY_ROWS, FLAG_NO_TMA = 0x8, 0x10, 0x20, 0x40
 FLAG_BUILD_JACOBI, FLAG_BUILD_STAIR = 0x100, 0x200
-FLAG_TMEM, FLAG_NO_TMEM, FLAG_TMEM_R2 = 0x400, 0x800, 0x1000
+FLAG_TMEM, FLAG_NO_TMEM, FLAG_TMEM_R2, FLAG_SYMMETRIC_S = 0x400, 0x800, 0x1000, 0x2000
 PINV_IDENTITY, PINV_JACOBI, PINV_STAIR = 0, 1, 2
 
 

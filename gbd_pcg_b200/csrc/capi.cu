@@ -17,10 +17,12 @@
 #include "pcg_fused.cuh"
 #include "pcg_tmem4.cuh"
 #include "pcg_generic.cuh"
+#include "pcg_grid.cuh"
 #include "pcg_rows.cuh"
 #include "pinv_build.h"
 #include "csr_pack.cuh"
 #include "schur_form.cuh"
+#include "sym_fill.cuh"
 
 namespace gbdpcg {
 
@@ -61,6 +63,7 @@ struct Plan {
     bool generic = false;
     bool fused_kernel = false;        // second-generation kernel (pcg_fused.cuh)
     bool tmem_kernel = false;         // tensor-memory batched kernel (pcg_tmem.cuh / pcg_tmem4.cuh)
+    bool grid_kernel = false;         // cooperative-grid kernel for systems beyond one cluster (pcg_grid.cuh); `cluster` = CTAs of the grid
     int tmem_per_sm = 0;              // CTAs of it that share an SM (tensor-memory columns, registers)
     int rpt = 1, fused = 0;           // rows per thread, single-reduction recurrence
     const RowsVariant *v = nullptr;
@@ -176,6 +179,50 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
     return false;
 }
 
+// Systems too large for one 16-CTA cluster: a cooperative grid of register-row CTAs, at most one per SM (pcg_grid.cuh).
+// The reference runs any N whose N CTAs are co-resident (include/pcg.cuh:23-49); this covers N up to SMs x block-rows per CTA.
+template <typename T>
+static bool plan_grid(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+{
+    constexpr bool f64 = sizeof(T) == 8;
+    if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK)) return false;      // single-reduction recurrence only
+    if (cfg.cluster) return false;
+    const GridVariant *tab = nullptr;
+    int cnt = 0;
+    switch (nx) {
+#define CASE(NX) case NX: tab = f64 ? grid_variants_f64_##NX(&cnt) : grid_variants_f32_##NX(&cnt); break;
+        GBDPCG_FOR_EACH_NX(CASE)
+#undef CASE
+        default: break;
+    }
+    if (cnt == 0) return false;
+    const int sms = device_sms();
+    int pm_opts[2] = {P_REG, P_SMEM};
+    int n_pm = 2;
+    if (!has_p) { pm_opts[0] = P_NONE; n_pm = 1; }
+    else if (cfg.flags & GBDPCG_FLAG_PINV_SMEM) { pm_opts[0] = P_SMEM; n_pm = 1; }
+    else if (cfg.flags & GBDPCG_FLAG_PINV_REG) { n_pm = 1; }
+    for (int ip = 0; ip < n_pm; ip++)
+        for (int i = 0; i < cnt; i++) {
+            const GridVariant *v = &tab[i];
+            if (v->pmode != pm_opts[ip]) continue;
+            const int tpb = (int)nx / v->rpt;
+            int bpc_max = v->maxt / tpb;
+            while (bpc_max > 0 && make_grid_plan<T>((int)nx, v->nxp, bpc_max, v->pmode).total > kMaxDynSmem) bpc_max--;
+            int bpc = ((int)N + sms - 1) / sms;                    // as many CTAs as there are SMs: the iteration is barrier-bound, not work-bound
+            const int bpc_2warps = (64 + tpb - 1) / tpb;           // ... but a CTA keeps at least two warps
+            if (bpc < bpc_2warps) bpc = bpc_2warps;
+            if (bpc > bpc_max) continue;
+            const int G = ((int)N + bpc - 1) / bpc;
+            out->generic = false; out->fused_kernel = false; out->tmem_kernel = false; out->grid_kernel = true; out->v = nullptr;
+            out->cluster = G; out->bpc = bpc; out->threads = round_up(bpc * tpb, 32); out->nbuf = 1; out->pmode = v->pmode;
+            out->smem = make_grid_plan<T>((int)nx, v->nxp, bpc, v->pmode).total; out->fn = v->fn; out->name = v->name; out->rpt = v->rpt;
+            out->fused = 1;
+            return true;
+        }
+    return false;
+}
+
 template <typename T>
 static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
 {
@@ -266,6 +313,8 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         }
     }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
+    // beyond one cluster: the cooperative-grid kernel, before the first-generation kernels get a say
+    if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_grid<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK;
     if (cnt > 0 && !(cfg.flags & GBDPCG_FLAG_FORCE_GENERIC)) {
         static const int cl_opts[] = {1, 2, 4, 8, 16};
         for (int cl : cl_opts) {
@@ -347,7 +396,11 @@ static int max_resident_problems(const Plan &p, int *out)
         *out = p.tmem_per_sm * sms;                        // bounded by tensor-memory columns and registers (plan_tmem), enforced through the shared-memory request
         return GBDPCG_OK;
     }
-    if (p.cluster == 1) {
+    if (p.grid_kernel) {
+        int per_sm = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p.fn, p.threads, p.smem));
+        *out = (per_sm * sms >= p.cluster) ? 1 : 0;       // the whole grid must be co-resident (cooperative launch); one system at a time
+    } else if (p.cluster == 1) {
         int per_sm = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p.fn, p.threads, p.smem));
         *out = per_sm * sms;
@@ -374,7 +427,7 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
                   uint32_t batch, const gbdpcg_config &cfg, uint32_t *d_iters, uint8_t *d_exits, cudaStream_t stream)
 {
     if (batch == 0) return GBDPCG_OK;
-    int rc = prepare_fn(p.fn, p.cluster > 1);
+    int rc = prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel);
     if (rc) return rc;
     int resident = 0;
     rc = max_resident_problems(p, &resident);
@@ -407,6 +460,36 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
             if ((rc = make_plan<T>(nx, N, P != nullptr, c2, batch, &p2))) return rc;
             return launch<T>(p2, S, P, gamma, lambda, nx, N, batch, c2, d_iters, d_exits, stream);
         }
+    }
+    if (p.grid_kernel) {
+        // one cooperative grid solves the systems of the batch one after the other; what crosses CTAs goes through a small
+        // stream-ordered scratch allocation (concurrent callers on other streams get their own)
+        KernelArgs<T> a;
+        a.S = S; a.Pinv = P; a.gamma = gamma; a.lambda = lambda; a.iters = d_iters; a.exits = d_exits;
+        a.mat_stride = 3ull * N * nx * nx; a.vec_stride = (unsigned long long)N * nx;
+        a.N = N; a.batch = batch; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg.max_iter; a.two_buffers = 0; a.use_tma = 0;
+        a.tol = (T)cfg.exit_tol;
+        const int G = p.cluster;
+        T *scratch = nullptr;
+        CK(cudaMallocAsync((void **)&scratch, grid_scratch_elems<T>((int)nx, G) * sizeof(T), stream));
+        GridScratch<T> gs;
+        gs.halo_r = scratch; gs.halo_rt = scratch + (size_t)G * 2 * nx; gs.halo_w = scratch + (size_t)G * 4 * nx;
+        gs.partials = scratch + (size_t)G * 6 * nx;
+        cudaLaunchConfig_t lc = {};
+        lc.gridDim = dim3((unsigned)G);
+        lc.blockDim = dim3(p.threads);
+        lc.dynamicSmemBytes = p.smem;
+        lc.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeCooperative;
+        at[0].val.cooperative = 1;
+        lc.attrs = at; lc.numAttrs = 1;
+        void *args[] = {&a, &gs};
+        const cudaError_t e = cudaLaunchKernelExC(&lc, p.fn, args);
+        cudaFreeAsync(scratch, stream);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaLaunchKernelExC (cooperative grid)", __LINE__);
+        g_launches.fetch_add(1, std::memory_order_relaxed);
+        return GBDPCG_OK;
     }
     const uint32_t n_groups = batch < (uint32_t)resident ? batch : (uint32_t)resident;
 
@@ -598,6 +681,25 @@ static int build_pinv_dev(const T *S, T *Pinv, uint32_t nx, uint32_t N, uint32_t
 template <typename T>
 static int build_pinv_host(gbdpcg_workspace *user_ws, const T *hS, T *hP, uint32_t nx, uint32_t N, uint32_t batch, int kind);
 
+// H2D of `n` systems of S.  GBDPCG_FLAG_SYMMETRIC_S: only the diagonal and right blocks cross PCIe (one strided copy, 2/3 of the
+// bytes); the left blocks are rebuilt on the device as transposes of the right blocks of the block-row above (sym_fill.cuh).
+template <typename T>
+static int upload_S(T *dS, const T *hS, uint32_t nx, uint32_t N, size_t n, const gbdpcg_config *cfg, cudaStream_t st)
+{
+    const size_t bb = (size_t)nx * nx;
+    if (!(cfg->flags & GBDPCG_FLAG_SYMMETRIC_S)) {
+        CK(cudaMemcpyAsync(dS, hS, sizeof(T) * 3 * bb * N * n, cudaMemcpyHostToDevice, st));
+        return GBDPCG_OK;
+    }
+    CK(cudaMemcpy2DAsync(dS + bb, sizeof(T) * 3 * bb, hS + bb, sizeof(T) * 3 * bb, sizeof(T) * 2 * bb, (size_t)N * n, cudaMemcpyHostToDevice, st));
+    const unsigned long long items = (unsigned long long)N * n;
+    const unsigned long long cap = (unsigned long long)device_sms() * 8;
+    sym_fill_left_kernel<T><<<(unsigned)(items < cap ? items : cap), 256, 0, st>>>(dS, nx, N, (uint32_t)n);
+    CK(cudaGetLastError());
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
 template <typename T>
 static int solve_batched_dev(const T *S, const T *Pinv, const T *gamma, T *lambda, uint32_t nx, uint32_t N, uint32_t batch,
                              const gbdpcg_config *cfg, uint32_t *d_iters, uint8_t *d_exits, void *stream)
@@ -646,7 +748,7 @@ static int solve_host(gbdpcg_workspace *user_ws, const T *hS, const T *hP, const
     if ((rc = ws_reserve(w, 3, vb))) return rc;
     cudaStream_t st = w->streams[0];
     StreamDrain drain{st};
-    CK(cudaMemcpyAsync(w->dbuf[0], hS, mb, cudaMemcpyHostToDevice, st));
+    if ((rc = upload_S<T>((T *)w->dbuf[0], hS, nx, N, 1, cfg, st))) return rc;
     if (bk >= 0) { if ((rc = build_pinv_dev<T>((const T *)w->dbuf[0], (T *)w->dbuf[1], nx, N, 1, bk, st))) return rc; }
     else if (has_p) CK(cudaMemcpyAsync(w->dbuf[1], hP, mb, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(w->dbuf[2], hg, vb, cudaMemcpyHostToDevice, st));
@@ -690,7 +792,7 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     Plan p;
     rc = make_plan<T>(nx, N, has_p, *cfg, batch, &p);
     if (rc) return rc;
-    if ((rc = prepare_fn(p.fn, p.cluster > 1))) return rc;
+    if ((rc = prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel))) return rc;
     int resident = 1;
     if ((rc = max_resident_problems(p, &resident))) return rc;
     if (resident < 1) resident = 1;
@@ -712,7 +814,7 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     for (size_t o = 0; o < batch; o += chunk, ci++) {
         const size_t n = (batch - o < chunk) ? batch - o : chunk;
         cudaStream_t st = w->streams[ci & 1];
-        CK(cudaMemcpyAsync(dS + o * me, hS + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
+        if ((rc = upload_S<T>(dS + o * me, hS + o * me, nx, N, n, cfg, st))) return rc;
         if (bk >= 0) { if ((rc = build_pinv_dev<T>(dS + o * me, dP + o * me, nx, N, (uint32_t)n, bk, st))) return rc; }
         else if (has_p) CK(cudaMemcpyAsync(dP + o * me, hP + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(dg + o * ve, hg + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
@@ -956,7 +1058,7 @@ static int plan_query(uint32_t nx, uint32_t N, int has_pinv, uint32_t batch, con
     int dev_count = 0;
     if (cudaGetDeviceCount(&dev_count) == cudaSuccess && dev_count > 0) {
         int res = 0;
-        if (prepare_fn(p.fn, p.cluster > 1) == GBDPCG_OK && max_resident_problems(p, &res) == GBDPCG_OK) out->max_resident = res;
+        if (prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel) == GBDPCG_OK && max_resident_problems(p, &res) == GBDPCG_OK) out->max_resident = res;
     } else {
         cudaGetLastError();
     }

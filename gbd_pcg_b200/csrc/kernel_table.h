@@ -58,4 +58,21 @@ GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_FUSED)
 GBDPCG_FOR_EACH_NX_EXTRA(GBDPCG_DECLARE_FUSED_EXTRA)
 #undef GBDPCG_DECLARE_FUSED_EXTRA
 
+// Cooperative-grid kernel (pcg_grid.cuh): one table per (dtype, nx).
+struct GridVariant {
+    int nx;
+    int is_f64;
+    int rpt;
+    int pmode;
+    int maxt;
+    int nxp;
+    const void *fn;
+    const char *name;
+};
+#define GBDPCG_DECLARE_GRID(NX)                              \
+    const GridVariant *grid_variants_f32_##NX(int *count);   \
+    const GridVariant *grid_variants_f64_##NX(int *count);
+GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_GRID)
+#undef GBDPCG_DECLARE_GRID
+
 }  // namespace gbdpcg

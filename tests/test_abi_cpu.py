@@ -73,6 +73,16 @@ def test_plan_query_without_gpu(nx, N, dtype, cluster, spec):
     assert 0 < info["smem_bytes"] <= 227 * 1024
 
 
+@pytest.mark.parametrize("nx,N,dtype", [(14, 1500, np.float32), (14, 1000, np.float64), (12, 1200, np.float32), (14, 833, np.float32), (14, 5328, np.float32)])
+def test_plan_query_beyond_one_cluster(nx, N, dtype):
+    """Systems no 16-CTA cluster holds go to the cooperative-grid kernel, at most one CTA per SM (the reference accepts any N whose
+    N CTAs are co-resident, include/pcg.cuh:23-49: 1776 knot points for nx=14 fp32 on a B200)."""
+    info = g.plan_query(nx, N, dtype, True)
+    assert "pcg_grid" in info["kernel"] and info["specialised"] == 1
+    assert info["cluster"] <= 148 and info["cluster"] * info["block_rows"] >= N
+    assert info["threads"] % 32 == 0 and 64 <= info["threads"] <= 1024 and 0 < info["smem_bytes"] <= 227 * 1024
+
+
 def test_plan_query_rejects_what_cannot_fit():
     with pytest.raises(g.GbdpcgError) as e:
         g.plan_query(14, 4096, np.float64, True)
