@@ -32,6 +32,9 @@
 #ifndef TMEM4_SCALAR_FMA
 #define TMEM4_SCALAR_FMA 0    // 1: scalar FFMA instead of the packed FFMA2 (A/B: a packed multiply-add reads three 64-bit register operands)
 #endif
+#ifndef TMEM4_STAGE_PAD
+#define TMEM4_STAGE_PAD 1     // staging stride per block-row padded (one bulk copy per block-row) so that the staging -> register gather is bank-conflict free
+#endif
 #ifndef TMEM4_L2_PREFETCH
 #define TMEM4_L2_PREFETCH 1   // pull the next system's S into L2 behind the iterations (its bulk copy into the one staging buffer is exposed)
 #endif
@@ -103,6 +106,20 @@ struct T4Geo {
     static constexpr int alloc_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : 256;
 };
 
+// Staging -> register gather.  A thread reads, per matrix column, rows 4g..4g+1 and 4g+2..4g+3 of its block-row with two 8-byte loads;
+// with the block-rows packed back to back (3nx^2 words apart) the 16 threads of a half-warp collide on the banks (nx = 14: 2.5
+// wavefronts per load on average, nx = 16: 4, nx = 8: 8).  Padding the staging stride by t4_stage_pad(nx) words and letting odd
+// block-rows read their two halves in the opposite order makes every load one wavefront (searched exhaustively over pads).
+__host__ __device__ constexpr int t4_stage_pad(int nx)
+{
+#if TMEM4_STAGE_PAD
+    return nx == 8 ? 4 : nx == 12 ? 4 : nx == 14 ? 12 : nx == 16 ? 8 : 0;
+#else
+    return 0;
+#endif
+}
+__host__ __device__ constexpr bool t4_stage_alt(int nx) { return t4_stage_pad(nx) != 0; }
+
 struct Tmem4Plan {
     uint32_t mbar_off, tbase_off, red_off, winA_off, winB_off, stage_off, total;
 };
@@ -115,7 +132,7 @@ __host__ __device__ inline Tmem4Plan make_tmem4_plan(int nx, int nxp, int N)
     p.red_off = o;   o += 2 * 8 * 4;                                     // 2 slots x 4 warps x (gamma, delta)
     p.winA_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
     p.winB_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
-    p.stage_off = o; o += (uint32_t)round_up(N * 3 * nx * nx * 4, 16);   // ONE matrix at a time
+    p.stage_off = o; o += (uint32_t)round_up(N * (3 * nx * nx + t4_stage_pad(nx)) * 4, 16) + 16;   // ONE matrix at a time (+ slack for the gather's dropped reads)
     p.total = o;
     return p;
 }
@@ -124,15 +141,21 @@ constexpr int kTmem4MaxThreads = 128;    // 4 warps: one per tensor-memory lane 
 // ---- a thread's share of one matrix, quad by quad (compile-time recursion over the quad index) ----
 // the 4 rows x W columns of quad Q from the staged block-row image (column-major nx x 3nx panel); rowp = first row of this thread
 template <class GEO, int NX, int Q>
-__device__ __forceinline__ void t4_gather_quad(const float *rowp, bool hi_ok, bool kill, float (&m)[4][4])
+__device__ __forceinline__ void t4_gather_quad(const float *rowp, bool hi_ok, bool swap, bool kill, float (&m)[4][4])
 {
     constexpr int j = Q / GEO::NQ, i = Q % GEO::NQ, W = GEO::qw(Q);
+    const int o1 = swap ? 2 : 0, o2 = 2 - o1;
 #pragma unroll
     for (int e = 0; e < W; e++) {
         const float *src = rowp + (j * NX + 4 * i + e) * NX;
-        const float2 lo = *reinterpret_cast<const float2 *>(src);
-        float2 hi = make_float2(0.f, 0.f);
-        if (hi_ok) hi = *reinterpret_cast<const float2 *>(src + 2);
+        // odd block-rows read their two halves in the opposite order (bank-conflict-free, t4_stage_pad).  Both loads are
+        // unconditional, so that the lanes of a half-warp issue each of them together; a thread whose upper half does not exist
+        // (rows >= nx) reads the next column's first rows (or the staging slack) and drops them.
+        const float2 a = *reinterpret_cast<const float2 *>(src + o1);
+        const float2 b = *reinterpret_cast<const float2 *>(src + o2);
+        const float2 lo = swap ? b : a;
+        float2 hi = swap ? a : b;
+        hi = hi_ok ? hi : make_float2(0.f, 0.f);
         m[0][e] = kill ? 0.f : lo.x;
         m[1][e] = kill ? 0.f : lo.y;
         m[2][e] = kill ? 0.f : hi.x;
@@ -141,7 +164,7 @@ __device__ __forceinline__ void t4_gather_quad(const float *rowp, bool hi_ok, bo
 }
 // staging -> registers (Mr[q]) or tensor memory (chunk register [row*W + e] = m(row, e)), quads Q .. NQT-1
 template <class GEO, int NX, bool IS_S, int Q>
-__device__ __forceinline__ void t4_load_matrix(const float *rowp, bool hi_ok, bool kill_left, bool kill_mid, bool kill_right, uint32_t tmine,
+__device__ __forceinline__ void t4_load_matrix(const float *rowp, bool hi_ok, bool swap, bool kill_left, bool kill_mid, bool kill_right, uint32_t tmine,
                                                float (&Mr)[GEO::NQT][4][4])
 {
     if constexpr (Q < GEO::NQT) {
@@ -149,7 +172,7 @@ __device__ __forceinline__ void t4_load_matrix(const float *rowp, bool hi_ok, bo
         const bool kill = (j == 0) ? kill_left : (j == 2) ? kill_right : kill_mid;
         if constexpr (GEO::in_tmem(IS_S, Q)) {
             float m[4][4];
-            t4_gather_quad<GEO, NX, Q>(rowp, hi_ok, kill, m);
+            t4_gather_quad<GEO, NX, Q>(rowp, hi_ok, swap, kill, m);
             uint32_t v[16];
 #pragma unroll
             for (int row = 0; row < 4; row++)
@@ -158,9 +181,9 @@ __device__ __forceinline__ void t4_load_matrix(const float *rowp, bool hi_ok, bo
             if constexpr (W == 4) tmem_st16(tmine + GEO::col(IS_S, Q), v);
             else tmem_st8(tmine + GEO::col(IS_S, Q), v);
         } else {
-            t4_gather_quad<GEO, NX, Q>(rowp, hi_ok, kill, Mr[Q]);
+            t4_gather_quad<GEO, NX, Q>(rowp, hi_ok, swap, kill, Mr[Q]);
         }
-        t4_load_matrix<GEO, NX, IS_S, Q + 1>(rowp, hi_ok, kill_left, kill_mid, kill_right, tmine, Mr);
+        t4_load_matrix<GEO, NX, IS_S, Q + 1>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Mr);
     }
 }
 // window quad Q (16-byte load, 8-byte for a half quad) and its packed multiply-adds: acc[row] += m(row, 0..W-1) . x(0..W-1)
@@ -298,15 +321,24 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     };
 
     const uint32_t mat_bytes = (uint32_t)(N * BSZ * (int)sizeof(T));
+    constexpr int SROW = BSZ + t4_stage_pad(NX);       // staging stride per block-row (words)
+    // matrix image -> staging, by warp 0: one bulk copy (packed staging) or one per block-row spread over the lanes (padded staging)
     auto issue_copy = [&](const T *src) {
-        mbar_expect_tx(mbar, mat_bytes);
-        bulk_g2s(smem_u32(stage), src, mat_bytes, mbar);
+        fence_proxy_async();
+        if (lane == 0) mbar_expect_tx(mbar, mat_bytes);
+        if constexpr (SROW == BSZ) {
+            if (lane == 0) bulk_g2s(smem_u32(stage), src, mat_bytes, mbar);
+        } else {
+            __syncwarp();
+            for (int k = lane; k < N; k += 32) bulk_g2s(smem_u32(stage + k * SROW), src + (size_t)k * BSZ, (uint32_t)(BSZ * sizeof(T)), mbar);
+        }
     };
     uint32_t phase = 0;
-    if (t == 0 && blockIdx.x < a.batch) issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride);
+    if (warp == 0 && blockIdx.x < a.batch) issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride);
 
     const bool kill_left = !active || b == 0, kill_right = !active || b == N - 1, kill_mid = !active;
-    const T *rowp = stage + (active ? lb * BSZ + 4 * g : 0);
+    const T *rowp = stage + (active ? lb * SROW + 4 * g : 0);
+    const bool swap = t4_stage_alt(NX) && (lb & 1);
 
     for (uint32_t prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
         const size_t vofs = (size_t)prob * a.vec_stride + (size_t)b * NX + 4 * g;
@@ -323,22 +355,21 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
         // ---- Phi^-1: staging -> tensor memory (registers for its first PQR quads) ----
         T Pr[NQT][4][4], Sr[NQT][4][4];               // only the quads that stay in registers are ever touched
         mbar_wait(mbar, phase); phase ^= 1;
-        t4_load_matrix<GEO, NX, false, 0>(rowp, hi_ok, kill_left, kill_mid, kill_right, tmine, Pr);
+        t4_load_matrix<GEO, NX, false, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Pr);
         __syncthreads();                                   // every thread has read its Phi^-1 rows: staging is free
-        if (t == 0) { fence_proxy_async(); issue_copy(a.S + (size_t)prob * a.mat_stride); }
+        if (warp == 0) issue_copy(a.S + (size_t)prob * a.mat_stride);
 
         // ---- S: staging -> registers (tensor memory for its last SQT quads) ----
         mbar_wait(mbar, phase); phase ^= 1;
-        t4_load_matrix<GEO, NX, true, 0>(rowp, hi_ok, kill_left, kill_mid, kill_right, tmine, Sr);
+        t4_load_matrix<GEO, NX, true, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Sr);
         tmem_wait_st();
         __syncthreads();                                   // staging is free again: fetch the next system's Phi^-1 behind the iterations
         {
             const uint32_t next = prob + gridDim.x;
-            if (t == 0 && next < a.batch) {
-                fence_proxy_async();
+            if (warp == 0 && next < a.batch) {
                 issue_copy(a.Pinv + (size_t)next * a.mat_stride);
 #if TMEM4_L2_PREFETCH
-                l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
+                if (lane == 0) l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
 #endif
             }
         }

@@ -48,5 +48,36 @@ def main(outdir):
                      source="reference pcg<T,nx,N> @75d6214 on NVIDIA B200, nvcc 12.9 -O3 sm_100a")
 
 
+def pinv_rows(N):
+    """Block-rows of Phi^-1 kept in a fixture: all of a small system, the first and last 8 of a long one (fixtures stay small)."""
+    return np.arange(N) if N <= 32 else np.concatenate([np.arange(8), np.arange(N - 8, N)])
+
+
+def main_pinv(outdir):
+    """Phi^-1 built by the reference's own primitives glass::invertMatrix / glass::gemm (GLASS/src/L3/inv.cuh:6-37, gemm.cuh) on the
+    blocks of S -> tests/golden/ref_glass_pinv_*.npz: what pins oracle_build_pinv_* and the product's pinv_build kernel."""
+    import gbd_pcg_b200 as g
+    os.makedirs(outdir, exist_ok=True)
+    for name, dtype in CASES:
+        S, _, _, nx, N, _, _ = make_system(name, "identity", dtype=dtype)
+        if not ref_cuda.has(dtype, nx, N) or not hasattr(ref_cuda.get(dtype, nx, N).L, "ref_glass_build_pinv"):
+            print("skip", name, np.dtype(dtype).name, "(no harness)")
+            continue
+        for kind in ("jacobi", "stair"):
+            P_ref = ref_cuda.get(dtype, nx, N).glass_build_pinv(S, kind)
+            P_o = oracle.build_pinv(S, nx, N, kind)
+            P_g = g.build_pinv_host(S, nx, N, 1, kind)
+            scale = np.abs(P_ref).max()
+            rows = pinv_rows(N)
+            print(f"{name} {np.dtype(dtype).name} {kind:6s} glass vs oracle max|d|/max|P| {np.abs(P_ref - P_o).max() / scale:.3e} | "
+                  f"glass vs pinv_build kernel {np.abs(P_ref - P_g).max() / scale:.3e} | bit-identical to oracle: {np.array_equal(P_ref, P_o)}", flush=True)
+            np.savez(os.path.join(outdir, f"ref_glass_pinv_{name}_{np.dtype(dtype).name}_{kind}.npz"),
+                     pinv_rows=P_ref.reshape(N, 3 * nx * nx)[rows], rows=rows, config=name, kind=kind, dtype=np.dtype(dtype).name, nx=nx, N=N,
+                     source="glass::invertMatrix + glass::gemm @GLASS a3e0931 on NVIDIA B200, nvcc 12.9 -O3 sm_100a, one CTA of 64 threads per block-row")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 2 and sys.argv[2] == "pinv":
+        main_pinv(sys.argv[1])
+        sys.exit(0)
     main(sys.argv[1] if len(sys.argv) > 1 else "gpurun_out/ref_fixtures")

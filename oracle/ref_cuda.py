@@ -58,6 +58,9 @@ class RefKernel:
         L.ref_solve_host.argtypes = [vp] * 3 + [C.c_uint32, C.c_double]
         L.ref_smem_bytes.restype = None
         L.ref_smem_bytes.argtypes = [C.POINTER(C.c_uint64)] * 2
+        if hasattr(L, "ref_glass_build_pinv"):
+            L.ref_glass_build_pinv.restype = C.c_int
+            L.ref_glass_build_pinv.argtypes = [vp, vp, C.c_int]
         L.ref_kernel_attrs.restype = C.c_int
         L.ref_kernel_attrs.argtypes = [C.POINTER(C.c_int)] * 2
         self.L = L
@@ -119,6 +122,18 @@ class RefKernel:
         """Scope H: the reference's host-pointer overload.  TIME ONLY: its d_Pinv is uninitialised (interface.cuh:45-46)."""
         vp = lambda a: a.ctypes.data_as(C.c_void_p)
         return int(self.L.ref_solve_host(vp(h_S), vp(h_gamma), vp(h_lambda), int(max_iter), float(tol)))
+
+    def glass_build_pinv(self, S, kind):
+        """Phi^-1 of one system from the reference's own primitives glass::invertMatrix / glass::gemm (GLASS/src/L3/inv.cuh:6-37,
+        gemm.cuh), one CTA per block-row.  kind: 'jacobi' | 'stair'."""
+        torch = self.torch
+        d_S = torch.from_numpy(np.ascontiguousarray(S, dtype=self.dtype)).cuda()
+        d_P = torch.empty_like(d_S)
+        torch.cuda.synchronize()
+        e = self.L.ref_glass_build_pinv(self._p(d_S), self._p(d_P), {"jacobi": 1, "stair": 2}[kind])
+        if e != 0:
+            raise RuntimeError(f"ref_glass_build_pinv failed: cudaError {e}")
+        return d_P.cpu().numpy()
 
     def attrs(self):
         r, b = C.c_int(), C.c_int()

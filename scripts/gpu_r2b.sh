@@ -5,6 +5,10 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm --format=csv,noheader
 scripts/ubench/ffma2_banks 2>&1 | tee gpurun_out/ffma2_banks_r2b.txt
 timeout 900 python scripts/time_tmem4.py 8192 all 2>&1 | tee gpurun_out/tmem4_r2b.txt
 GBDPCG_LIB=$PWD/gbd_pcg_b200/variants/libgbdpcg_scalar.so TMEM4_ARMS=tmem4_v0,tmem4_v1,tmem4_v3 timeout 600 python scripts/time_tmem4.py 8192 c5 2>&1 | tee gpurun_out/tmem4_scalar_r2b.txt
+GBDPCG_LIB=$PWD/gbd_pcg_b200/variants/libgbdpcg_nopad.so TMEM4_ARMS=auto timeout 600 python scripts/time_tmem4.py 8192 all 2>&1 | tee gpurun_out/tmem4_nopad_r2b.txt
+timeout 300 python scripts/time_grid.py 2>&1 | tee gpurun_out/grid_r2b.txt
+timeout 300 python scripts/time_tail.py 2>&1 | tee gpurun_out/tail_r2b.txt
+timeout 600 python oracle/make_ref_fixtures.py gpurun_out/ref_fixtures pinv 2>&1 | tee gpurun_out/ref_glass_pinv_fixtures.log
 LD_LIBRARY_PATH=$PWD/gbd_pcg_b200 timeout 300 examples/api_surface.exe 2>&1 | tee gpurun_out/api_surface_r2b.txt
 timeout 600 python -c "import __graft_entry__ as e; e.smoke()" 2>&1 | tail -8 | tee gpurun_out/smoke_r2b.txt
 timeout 1500 python -m pytest tests -q -m gpu 2>&1 | tail -25 | tee gpurun_out/pytest_gpu_r2b.txt

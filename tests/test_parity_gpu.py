@@ -517,6 +517,28 @@ def test_symmetric_s_shipping(dt):
     assert it1 == it_f[1] and np.array_equal(l1, lam_f[1])
 
 
+def test_fp64_batch_at_bench_size():
+    """The fp64 leg of bench.py (other_configs.C3_batched): 2048 x C3 (nx 14, N 64, fp64, tol 1e-10, stair), 64 distinct seeds tiled;
+    every distinct system against the oracle at the fp64 bar, replicas bit-identical wherever they ran."""
+    torch = _torch()
+    nx, nu, N, dt, tol, max_iter = g.synth.CONFIGS["C3"]
+    batch, nseed = 2048, 64
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", dt)
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // nseed, 1) for a in (S, P, gam))
+    d_l = torch.zeros(batch, N * nx, dtype=torch.float64, device="cuda")
+    d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+    d_ex = torch.ones(batch, dtype=torch.uint8, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0)
+    g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, d_ex)
+    torch.cuda.synchronize()
+    assert int(d_ex.sum().item()) == 0
+    lam, its = d_l.cpu().numpy(), d_it.cpu().numpy()
+    for s_ in range(nseed):
+        block = lam[s_::nseed]
+        assert (block == block[0]).all() and (its[s_::nseed] == its[s_]).all()
+        check_against_oracle(S[s_], P[s_], gam[s_], np.zeros(N * nx, dt), nx, N, tol, max_iter, lam[s_], int(its[s_]), False)
+
+
 def test_full_size_batch_properties():
     """BASELINE C5 size (8192 x C2) through size-independent properties: the residual of every returned
     lambda satisfies the exit criterion's neighbourhood and S*lambda reproduces gamma (checked by the oracle's

@@ -77,3 +77,37 @@ def test_stair_preconditioner_from_the_oracle_drives_the_solve():
         P = oracle.build_pinv(S, nx, N, kind)
         _, it, ex = oracle.pcg(S, P, gam, np.zeros(N * nx, np.float32), nx, N, 1e-6, 1000)
         assert not ex and abs(it - iters) <= 1
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the builder oracle held to the reference's OWN primitives: tests/golden/ref_glass_pinv_*.npz were recorded by running
+# glass::invertMatrix / glass::gemm (reference GLASS/src/L3/inv.cuh:6-37, gemm.cuh) on the blocks of S on a B200
+# (oracle/ref_harness.cu: ref_glass_build_pinv; oracle/make_ref_fixtures.py <dir> pinv)
+# ---------------------------------------------------------------------------------------------------------------
+import glob  # noqa: E402
+import os  # noqa: E402
+
+from conftest import GOLDEN  # noqa: E402
+from helpers import make_system  # noqa: E402
+
+GLASS_FIXTURES = sorted(glob.glob(os.path.join(GOLDEN, "ref_glass_pinv_*.npz")))
+GLASS_BAR = {np.dtype(np.float32): 2e-5, np.dtype(np.float64): 1e-11}      # same order of operations; FMA contraction differs (GPU vs x86)
+
+
+@pytest.mark.skipif(not GLASS_FIXTURES, reason="no glass::invertMatrix fixtures recorded yet")
+@pytest.mark.parametrize("path", GLASS_FIXTURES, ids=lambda p: os.path.basename(p)[len("ref_glass_pinv_"):-len(".npz")])
+def test_oracle_builder_matches_recorded_glass_outputs(path):
+    z = np.load(path)
+    name, kind, dtype = str(z["config"]), str(z["kind"]), np.dtype(str(z["dtype"]))
+    S, _, _, nx, N, _, _ = make_system(name, "identity", dtype=dtype.type)
+    assert (nx, N) == (int(z["nx"]), int(z["N"]))
+    P = oracle.build_pinv(S, nx, N, kind).reshape(N, 3 * nx * nx)[z["rows"]]
+    ref = z["pinv_rows"]
+    assert ref.dtype == dtype and np.isfinite(ref).all()
+    assert float(np.abs(P.astype(np.float64) - ref).max() / np.abs(ref).max()) < GLASS_BAR[dtype]
+    # the recorded preconditioner really is one: diagonal blocks invert those of S
+    Sb = S.reshape(N, 3, nx, nx)
+    for i, k in enumerate(z["rows"][:3]):
+        D = Sb[k, 1].T.astype(np.float64)                                  # column-major block
+        Dinv = ref[i].reshape(3, nx, nx)[1].T.astype(np.float64)
+        assert np.abs(D @ Dinv - np.eye(nx)).max() < (5e-4 if dtype == np.float32 else 1e-10)

@@ -257,3 +257,46 @@ def test_zero_batch_is_a_no_op():
     before = g.kernel_launches()
     g.build_pinv_dev(4, 2, 0, x, x.clone(), "stair")
     assert g.kernel_launches() == before
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the product's builder kernel held to the reference's own primitives (glass::invertMatrix / glass::gemm): recorded fixtures, and
+# the live harness when it travelled with the repo
+# ---------------------------------------------------------------------------------------------------------------
+import glob  # noqa: E402
+import os  # noqa: E402
+
+from conftest import GOLDEN  # noqa: E402
+
+GLASS_FIXTURES = sorted(glob.glob(os.path.join(GOLDEN, "ref_glass_pinv_*.npz")))
+
+
+@pytest.mark.skipif(not GLASS_FIXTURES, reason="no glass::invertMatrix fixtures recorded yet")
+@pytest.mark.parametrize("path", GLASS_FIXTURES, ids=lambda p: os.path.basename(p)[len("ref_glass_pinv_"):-len(".npz")])
+def test_builder_kernel_matches_recorded_glass_outputs(path):
+    z = np.load(path)
+    name, kind, dtype = str(z["config"]), str(z["kind"]), np.dtype(str(z["dtype"]))
+    S, _, _, nx, N, _, _ = make_system(name, "identity", dtype=dtype.type)
+    P = gpu_build(S, nx, N, 1, kind).reshape(N, 3 * nx * nx)[z["rows"]]
+    assert max_rel(P, z["pinv_rows"]) < BAR[dtype]
+
+
+@pytest.mark.parametrize("name,dtype", [("C1", np.float32), ("C1", np.float64), ("C2", np.float32), ("C3", np.float64), ("C4", np.float32)])
+@pytest.mark.parametrize("kind", ["jacobi", "stair"])
+def test_builder_kernel_against_live_glass_primitives(name, dtype, kind):
+    from oracle import ref_cuda
+    S, _, _, nx, N, _, _ = make_system(name, "identity", dtype=dtype)
+    if not ref_cuda.has(dtype, nx, N) or not hasattr(ref_cuda.get(dtype, nx, N).L, "ref_glass_build_pinv"):
+        pytest.skip("reference harness not built for this config")
+    P_ref = ref_cuda.get(dtype, nx, N).glass_build_pinv(S, kind)
+    P = gpu_build(S, nx, N, 1, kind)
+    assert max_rel(P, P_ref) < BAR[np.dtype(dtype)]
+    assert max_rel(oracle.build_pinv(S, nx, N, kind), P_ref) < BAR[np.dtype(dtype)]
+    # a solve preconditioned with the reference-built Phi^-1 and one with ours take the same number of iterations
+    if name != "C1":
+        _, _, gam, _, _, tol, max_iter = make_system(name, "identity", dtype=dtype)
+        cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0)
+        l1, l2 = np.zeros(N * nx, dtype), np.zeros(N * nx, dtype)
+        it1 = g.solvePCG(S, gam, l1, nx, N, cfg, h_Pinv=P_ref)
+        it2 = g.solvePCG(S, gam, l2, nx, N, cfg, h_Pinv=P)
+        assert abs(it1 - it2) <= 1
