@@ -68,6 +68,7 @@ struct Plan {
     int rpt = 1, fused = 0;           // rows per thread, single-reduction recurrence
     const RowsVariant *v = nullptr;
     int cluster = 1, bpc = 0, threads = 0, nbuf = 1, pmode = P_NONE;
+    int base_cluster = 1;             // cluster size the planner fitted before latency mode promoted it (pcg_fused)
     size_t smem = 0;
     const void *fn = nullptr;
     const char *name = "";
@@ -153,7 +154,7 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
                 if (smem > kMaxDynSmem) continue;
                 out->generic = false; out->fused_kernel = true; out->v = nullptr; out->cluster = cl; out->bpc = bpc;
                 out->threads = threads; out->nbuf = (v->pmode == P_REG) ? 2 : 1; out->pmode = v->pmode; out->smem = smem;
-                out->fn = v->fn; out->name = v->name; out->rpt = v->rpt; out->fused = v->fused;
+                out->fn = v->fn; out->name = v->name; out->rpt = v->rpt; out->fused = v->fused; out->base_cluster = cl;
                 // Latency mode.  A system that needs a cluster anyway solves faster on a LARGER one -- fewer rows per CTA,
                 // and with the push-mode exchanges a CTA more costs nothing (C3: 63.5 us on 4 CTAs, 55.3 on 16; nx=24,N=64:
                 // 88 -> 55; profiles/clusters_r1e.txt) -- as long as every system of the batch still gets its own cluster in
@@ -432,6 +433,21 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
     int resident = 0;
     rc = max_resident_problems(p, &resident);
     if (rc) return rc;
+    if (p.fused_kernel && p.cluster > p.base_cluster && (resident < 1 || (uint32_t)resident < batch)) {
+        // Latency mode promoted this plan to a larger (possibly non-portable 16-CTA) cluster on the strength of SM arithmetic alone.
+        // If that many clusters cannot be co-resident after all (MIG slice, fewer SMs per GPC, another tenant on the GPCs), step
+        // down towards the cluster size the planner had fitted first instead of failing or running a second pass.
+        Plan q = p;
+        while (q.cluster > p.base_cluster) {
+            q.cluster >>= 1;
+            q.bpc = ((int)N + q.cluster - 1) / q.cluster;
+            q.threads = round_up(q.bpc * ((int)nx / q.rpt), 32);
+            q.smem = make_fused_plan<T>((int)nx, Geo<T>::nxp((int)nx), q.bpc, q.pmode, q.pmode == P_REG ? 2 : 1).total;
+            int r2 = 0;
+            if (max_resident_problems(q, &r2) == GBDPCG_OK && r2 >= 1 && ((uint32_t)r2 >= batch || q.cluster == p.base_cluster))
+                return launch<T>(q, S, P, gamma, lambda, nx, N, batch, cfg, d_iters, d_exits, stream);
+        }
+    }
     if (resident < 1)
         return fail(GBDPCG_ERR_UNSUPPORTED, "kernel %s cannot become resident (cluster=%d threads=%d smem=%zu)", p.name, p.cluster,
                     p.threads, p.smem);

@@ -1,6 +1,6 @@
 // pcg_generic.cuh -- runtime-nx fallback kernel (any state size / horizon that fits one SM's shared memory).
 //
-// Used only when no register-row kernel (pcg_rows.cuh) is compiled for the requested nx.  One CTA per
+// Used only when no specialised kernel (pcg_fused.cuh: nx <= 32, fp64 <= 25) is compiled for the requested nx.  One CTA per
 // system, persistent over the batch; lambda, r, p, r~ live in shared memory, S and Phi^-1 are streamed
 // from global memory (L2-resident after the first iteration) with row-consecutive, coalesced loads.
 // Same recurrence and exit semantics as the fast path (reference include/pcg.cuh:118-212); same

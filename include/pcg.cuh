@@ -1,8 +1,9 @@
 // pcg.cuh -- launch-sizing helpers of the drop-in headers.
 //
 // The reference's include/pcg.cuh holds its kernel plus two host helpers, pcgSharedMemSize<T>
-// (:13-20) and checkPcgOccupancy<T> (:23-49).  The kernel of this build lives in libgbdpcg.so
-// (gbd_pcg_b200/csrc/pcg_rows.cuh); the two helpers keep their names and answer for the kernel this
+// (:13-20) and checkPcgOccupancy<T> (:23-49).  The kernels of this build live in libgbdpcg.so
+// (gbd_pcg_b200/csrc: pcg_fused.cuh for one system per CTA / cluster, pcg_tmem4.cuh / pcg_tmem.cuh for fp32 batches,
+// pcg_grid.cuh beyond one cluster); the two helpers keep their names and answer for the kernel this
 // library would actually launch, through gbdpcg_plan_query.
 #pragma once
 #include <cstdint>
@@ -39,8 +40,8 @@ size_t pcgSharedMemSize(uint32_t state_size, uint32_t knot_points)
 
 // True when one system of this shape can be made resident on the current device.  `kernel` and `block`
 // are accepted for source compatibility and ignored (the library picks its own kernel and launch shape).
-// Exit statuses follow the reference: 5 = device lacks the required launch capability (here:
-// thread-block clusters, i.e. compute capability < 9.0), 6 = the system does not fit.
+// Exit statuses follow the reference: 5 = device lacks the required launch capability (here: not a
+// Blackwell GPU -- the library is built for sm_100a only, compute capability major < 10), 6 = the system does not fit.
 template <typename T>
 bool checkPcgOccupancy(void * /*kernel*/, dim3 /*block*/, uint32_t state_size, uint32_t knot_points)
 {
