@@ -290,7 +290,7 @@ def run_ours(args):
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     lam_c = np.zeros((nloc, N_KNOT * NX), dtype=DTYPE)
     t0 = time.perf_counter()
-    _, it_c, _ = oracle.pcg_batched(S, P, gam, lam_c, NX, N_KNOT, TOL, MAX_ITER, order=0, threads=cores)
+    lam_c, it_c, _ = oracle.pcg_batched(S, P, gam, lam_c, NX, N_KNOT, TOL, MAX_ITER, order=0, threads=cores)
     t_cpu = time.perf_counter() - t0
     d_iters = np.abs(iters.astype(np.int64) - it_c.astype(np.int64))
     same = d_iters == 0

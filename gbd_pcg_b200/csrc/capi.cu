@@ -423,6 +423,32 @@ static int max_resident_problems(const Plan &p, int *out)
     return GBDPCG_OK;
 }
 
+// Stream-ordered scratch for the cooperative-grid kernel comes from a pool of this library's own, one per device, that keeps its
+// memory between launches: the device's default pool releases everything at the next synchronisation point (release threshold 0),
+// which made every launch pay ~0.75 ms of allocator work (profiles/grid_r2b.txt).
+static int scratch_pool(cudaMemPool_t *out)
+{
+    static std::mutex mu;
+    static std::vector<std::pair<int, cudaMemPool_t>> pools;
+    int dev;
+    CK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    for (auto &e : pools)
+        if (e.first == dev) { *out = e.second; return GBDPCG_OK; }
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = dev;
+    cudaMemPool_t pool;
+    CK(cudaMemPoolCreate(&pool, &props));
+    unsigned long long keep = ~0ull;
+    CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    pools.push_back({dev, pool});
+    *out = pool;
+    return GBDPCG_OK;
+}
+
 template <typename T>
 static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lambda, uint32_t nx, uint32_t N,
                   uint32_t batch, const gbdpcg_config &cfg, uint32_t *d_iters, uint8_t *d_exits, cudaStream_t stream)
@@ -487,7 +513,9 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
         a.tol = (T)cfg.exit_tol;
         const int G = p.cluster;
         T *scratch = nullptr;
-        CK(cudaMallocAsync((void **)&scratch, grid_scratch_elems<T>((int)nx, G) * sizeof(T), stream));
+        cudaMemPool_t pool;
+        if ((rc = scratch_pool(&pool))) return rc;
+        CK(cudaMallocFromPoolAsync((void **)&scratch, grid_scratch_elems<T>((int)nx, G) * sizeof(T), pool, stream));
         GridScratch<T> gs;
         gs.halo_r = scratch; gs.halo_rt = scratch + (size_t)G * 2 * nx; gs.halo_w = scratch + (size_t)G * 4 * nx;
         gs.partials = scratch + (size_t)G * 6 * nx;

@@ -41,6 +41,19 @@
 
 namespace gbdpcg {
 
+#ifdef TMEM4_TRACE
+// phase timeline (scripts/ubench/trace_tmem4.cu): clock64() of thread 0 of the first 8 CTAs -- per system (ordinal within the CTA):
+// 0 top, 1 Phi^-1 arrived, 2 Phi^-1 in tensor memory, 3 S arrived, 4 S in registers, 5 prologue done, 6 loop left, 7 outputs written;
+// per iteration of the 6th system: 0 top, 1 r~ done, 2 w done, 3 reduction done, 4 updates done
+__device__ long long g_t4sys[8][40][8];
+__device__ long long g_t4it[8][48][5];
+#define T4S(m) do { if (t == 0 && blockIdx.x < 8 && sys_ord < 40) g_t4sys[blockIdx.x][sys_ord][m] = clock64(); } while (0)
+#define T4I(m) do { if (t == 0 && blockIdx.x < 8 && sys_ord == 5 && it < 48) g_t4it[blockIdx.x][it][m] = clock64(); } while (0)
+#else
+#define T4S(m) do { } while (0)
+#define T4I(m) do { } while (0)
+#endif
+
 __device__ __forceinline__ void tmem_ld8(uint32_t taddr, uint32_t (&v)[16])
 {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
@@ -108,12 +121,12 @@ struct T4Geo {
 
 // Staging -> register gather.  A thread reads, per matrix column, rows 4g..4g+1 and 4g+2..4g+3 of its block-row with two 8-byte loads;
 // with the block-rows packed back to back (3nx^2 words apart) the 16 threads of a half-warp collide on the banks (nx = 14: 2.5
-// wavefronts per load on average, nx = 16: 4, nx = 8: 8).  Padding the staging stride by t4_stage_pad(nx) words and letting odd
+// wavefronts per load on average, nx = 16: 4, nx = 8: 8; measured on 8192 systems: nx = 16, N = 30 0.91 -> 0.80 ms, nx = 8, N = 60 0.72 -> 0.64).  Padding the staging stride by t4_stage_pad(nx) words and letting odd
 // block-rows read their two halves in the opposite order makes every load one wavefront (searched exhaustively over pads).
 __host__ __device__ constexpr int t4_stage_pad(int nx)
 {
 #if TMEM4_STAGE_PAD
-    return nx == 8 ? 4 : nx == 12 ? 4 : nx == 14 ? 12 : nx == 16 ? 8 : 0;
+    return nx == 8 ? 4 : nx == 14 ? 12 : nx == 16 ? 8 : 0;      // (nx = 12: the searched pad saves a third of the wavefronts and measured slower, 0.80 vs 0.75 ms)
 #else
     return 0;
 #endif
@@ -196,6 +209,16 @@ __device__ __forceinline__ float4 t4_window_quad(const float *w)
         const float2 h = *reinterpret_cast<const float2 *>(w + j * NXP + 4 * i);
         return make_float4(h.x, h.y, 0.f, 0.f);
     }
+}
+// 1 / x to within an ulp: MUFU.RCP + one Newton step, branch-free (a plain division expands into a range check with a slow-path
+// call; the scalars of an iteration sit on every warp's critical path).  Operands here are dot products far from the denormal range;
+// a zero or NaN operand yields inf / NaN like the division it replaces (alpha = NaN never converges: reference semantics).
+__device__ __forceinline__ float t4_rcp(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    const float e = fmaf(-x, r, 1.f);
+    return isfinite(e) ? fmaf(r, e, r) : r;
 }
 // acc += (m0, m1) * (x0, x1), packed (FFMA2) or as two scalar FFMAs
 __device__ __forceinline__ void t4_fma2(float2 &acc, float m0, float m1, float x0, float x1)
@@ -340,7 +363,11 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     const T *rowp = stage + (active ? lb * SROW + 4 * g : 0);
     const bool swap = t4_stage_alt(NX) && (lb & 1);
 
+    int sys_ord = -1;
+    (void)sys_ord;
     for (uint32_t prob = blockIdx.x; prob < a.batch; prob += gridDim.x) {
+        ++sys_ord;
+        T4S(0);
         const size_t vofs = (size_t)prob * a.vec_stride + (size_t)b * NX + 4 * g;
         T lam[R] = {0.f, 0.f, 0.f, 0.f}, gam[R] = {0.f, 0.f, 0.f, 0.f};
         if (active) {
@@ -355,15 +382,19 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
         // ---- Phi^-1: staging -> tensor memory (registers for its first PQR quads) ----
         T Pr[NQT][4][4], Sr[NQT][4][4];               // only the quads that stay in registers are ever touched
         mbar_wait(mbar, phase); phase ^= 1;
+        T4S(1);
         t4_load_matrix<GEO, NX, false, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Pr);
         __syncthreads();                                   // every thread has read its Phi^-1 rows: staging is free
+        T4S(2);
         if (warp == 0) issue_copy(a.S + (size_t)prob * a.mat_stride);
 
         // ---- S: staging -> registers (tensor memory for its last SQT quads) ----
         mbar_wait(mbar, phase); phase ^= 1;
+        T4S(3);
         t4_load_matrix<GEO, NX, true, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Sr);
         tmem_wait_st();
         __syncthreads();                                   // staging is free again: fetch the next system's Phi^-1 behind the iterations
+        T4S(4);
         {
             const uint32_t next = prob + gridDim.x;
             if (warp == 0 && next < a.batch) {
@@ -407,28 +438,34 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
         uint32_t it = 0;
         bool hit_max = true;
         T rcp_gamma = 0.f, rcp_alpha = 0.f;
+        T4S(5);
         for (;;) {
+            T4I(0);
             publish(winA, res);
             t4_tmem_ld<GEO, false, 0>(tmine, u0);
             __syncthreads();
             mv_P(winA, u0, rt);                   // r~ = Phi^-1 r                (pcg.cuh:131-140, 181-184)
+            T4I(1);
             publish(winB, rt);
             t4_tmem_ld<GEO, true, 0>(tmine, u0);
             __syncthreads();
             mv_S(winB, u0, w);                       // w = S r~
+            T4I(2);
             T gg = 0.f, dd = 0.f;
 #pragma unroll
             for (int i = 0; i < R; i++) { gg += res[i] * rt[i]; dd += w[i] * rt[i]; }
             const Pair<T> gd = all_sum(gg, dd);            // gamma = r.r~ , delta = w.r~
             const T gamma = gd.x(), delta = gd.y();
+            T4I(3);
             if (it > 0 && abs_t(gamma) < a.tol) { hit_max = false; break; }   // reference exit test (pcg.cuh:195)
             if (it == a.max_iter) break;
-            T beta, alpha;
-            if (it == 0) { beta = 0.f; alpha = gamma / delta; }
-            else {
-                beta = gamma * rcp_gamma;
-                alpha = gamma / (delta - beta * (gamma * rcp_alpha));
-            }
+            // beta = gamma / gamma_old, alpha = gamma / (delta - beta * gamma / alpha_old).  Both divisions of an iteration are
+            // reciprocals of numbers known right after the reduction (gamma and the denominator), so they are issued together;
+            // 1 / alpha for the next iteration is denominator / gamma, no third division.
+            const T rg = t4_rcp(gamma);
+            const T beta = (it == 0) ? 0.f : gamma * rcp_gamma;
+            const T denom = (it == 0) ? delta : delta - beta * (gamma * rcp_alpha);
+            const T alpha = gamma * t4_rcp(denom);
 #pragma unroll
             for (int i = 0; i < R; i++) {
                 p[i] = rt[i] + beta * p[i];
@@ -436,11 +473,13 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
                 s[i] = w[i] + beta * s[i];
                 res[i] -= alpha * s[i];
             }
-            rcp_gamma = 1.f / gamma;
-            rcp_alpha = 1.f / alpha;
+            rcp_gamma = rg;
+            rcp_alpha = denom * rg;
+            T4I(4);
             ++it;
         }
 
+        T4S(6);
         // ---- outputs                                                            (pcg.cuh:212-215) ----
         if (active) {
             a.lambda[vofs] = lam[0]; a.lambda[vofs + 1] = lam[1];
@@ -450,6 +489,7 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
             if (a.iters) a.iters[prob] = it;
             if (a.exits) a.exits[prob] = hit_max ? 1 : 0;
         }
+        T4S(7);
     }
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
