@@ -121,17 +121,22 @@ struct T4Geo {
 
 // Staging -> register gather.  A thread reads, per matrix column, rows 4g..4g+1 and 4g+2..4g+3 of its block-row with two 8-byte loads;
 // with the block-rows packed back to back (3nx^2 words apart) the 16 threads of a half-warp collide on the banks (nx = 14: 2.5
-// wavefronts per load on average, nx = 16: 4, nx = 8: 8; measured on 8192 systems: nx = 16, N = 30 0.91 -> 0.80 ms, nx = 8, N = 60 0.72 -> 0.64).  Padding the staging stride by t4_stage_pad(nx) words and letting odd
-// block-rows read their two halves in the opposite order makes every load one wavefront (searched exhaustively over pads).
+// wavefronts per load on average, nx = 16: 4, nx = 8: 8).  The staging image is therefore laid out in PAIRS of block-rows with
+// t4_stage_pad(nx) words between pairs (one bulk copy per pair), and even block-rows read their two halves in the opposite order:
+// every load is then one wavefront (layouts searched exhaustively; measured on 8192 systems: nx = 16, N = 30 0.91 -> 0.80 ms,
+// nx = 8, N = 60 0.72 -> 0.64).  nx = 10, 12 (three threads per block-row) stay packed: the best layout found saves a third of the
+// wavefronts and measured slower.
 __host__ __device__ constexpr int t4_stage_pad(int nx)
 {
 #if TMEM4_STAGE_PAD
-    return nx == 8 ? 4 : nx == 14 ? 12 : nx == 16 ? 8 : 0;      // (nx = 12: the searched pad saves a third of the wavefronts and measured slower, 0.80 vs 0.75 ms)
+    return nx == 8 ? 8 : nx == 14 ? 24 : nx == 16 ? 16 : 0;
 #else
     return 0;
 #endif
 }
 __host__ __device__ constexpr bool t4_stage_alt(int nx) { return t4_stage_pad(nx) != 0; }
+// words from the start of the staging image to block-row lb
+__host__ __device__ constexpr int t4_stage_ofs(int nx, int lb) { return lb * 3 * nx * nx + (lb >> 1) * t4_stage_pad(nx); }
 
 struct Tmem4Plan {
     uint32_t mbar_off, tbase_off, red_off, winA_off, winB_off, stage_off, total;
@@ -145,7 +150,7 @@ __host__ __device__ inline Tmem4Plan make_tmem4_plan(int nx, int nxp, int N)
     p.red_off = o;   o += 2 * 8 * 4;                                     // 2 slots x 4 warps x (gamma, delta)
     p.winA_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
     p.winB_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
-    p.stage_off = o; o += (uint32_t)round_up(N * (3 * nx * nx + t4_stage_pad(nx)) * 4, 16) + 16;   // ONE matrix at a time (+ slack for the gather's dropped reads)
+    p.stage_off = o; o += (uint32_t)round_up(t4_stage_ofs(nx, N + 1) * 4, 16) + 16;   // ONE matrix at a time (+ slack for the gather's dropped reads)
     p.total = o;
     return p;
 }
@@ -161,7 +166,7 @@ __device__ __forceinline__ void t4_gather_quad(const float *rowp, bool hi_ok, bo
 #pragma unroll
     for (int e = 0; e < W; e++) {
         const float *src = rowp + (j * NX + 4 * i + e) * NX;
-        // odd block-rows read their two halves in the opposite order (bank-conflict-free, t4_stage_pad).  Both loads are
+        // even block-rows read their two halves in the opposite order (bank-conflict-free, t4_stage_pad).  Both loads are
         // unconditional, so that the lanes of a half-warp issue each of them together; a thread whose upper half does not exist
         // (rows >= nx) reads the next column's first rows (or the staging slack) and drops them.
         const float2 a = *reinterpret_cast<const float2 *>(src + o1);
@@ -344,24 +349,32 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     };
 
     const uint32_t mat_bytes = (uint32_t)(N * BSZ * (int)sizeof(T));
-    constexpr int SROW = BSZ + t4_stage_pad(NX);       // staging stride per block-row (words)
-    // matrix image -> staging, by warp 0: one bulk copy (packed staging) or one per block-row spread over the lanes (padded staging)
+    // matrix image -> staging: one bulk copy (packed staging, thread 0), or one per pair of block-rows spread over the warps (padded
+    // staging: a bulk copy is issued lane by lane, so the pairs are dealt to the warps first).  Called by every thread.
     auto issue_copy = [&](const T *src) {
-        fence_proxy_async();
-        if (lane == 0) mbar_expect_tx(mbar, mat_bytes);
-        if constexpr (SROW == BSZ) {
-            if (lane == 0) bulk_g2s(smem_u32(stage), src, mat_bytes, mbar);
+        if constexpr (t4_stage_pad(NX) == 0) {
+            if (t == 0) {
+                fence_proxy_async();
+                mbar_expect_tx(mbar, mat_bytes);
+                bulk_g2s(smem_u32(stage), src, mat_bytes, mbar);
+            }
         } else {
-            __syncwarp();
-            for (int k = lane; k < N; k += 32) bulk_g2s(smem_u32(stage + k * SROW), src + (size_t)k * BSZ, (uint32_t)(BSZ * sizeof(T)), mbar);
+            const int nwarps = (int)blockDim.x >> 5, npairs = (N + 1) >> 1;
+            const int c = warp + nwarps * lane;                       // pair of block-rows this lane copies
+            if (t == 0) mbar_expect_tx(mbar, mat_bytes);
+            if (c < npairs) {
+                fence_proxy_async();
+                const int rows = (2 * c + 2 <= N) ? 2 : 1;
+                bulk_g2s(smem_u32(stage + t4_stage_ofs(NX, 2 * c)), src + (size_t)(2 * c) * BSZ, (uint32_t)(rows * BSZ * sizeof(T)), mbar);
+            }
         }
     };
     uint32_t phase = 0;
-    if (warp == 0 && blockIdx.x < a.batch) issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride);
+    if (blockIdx.x < a.batch) issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride);
 
     const bool kill_left = !active || b == 0, kill_right = !active || b == N - 1, kill_mid = !active;
-    const T *rowp = stage + (active ? lb * SROW + 4 * g : 0);
-    const bool swap = t4_stage_alt(NX) && (lb & 1);
+    const T *rowp = stage + (active ? t4_stage_ofs(NX, lb) + 4 * g : 0);
+    const bool swap = t4_stage_alt(NX) && !(lb & 1);
 
     int sys_ord = -1;
     (void)sys_ord;
@@ -386,7 +399,7 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
         t4_load_matrix<GEO, NX, false, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Pr);
         __syncthreads();                                   // every thread has read its Phi^-1 rows: staging is free
         T4S(2);
-        if (warp == 0) issue_copy(a.S + (size_t)prob * a.mat_stride);
+        issue_copy(a.S + (size_t)prob * a.mat_stride);
 
         // ---- S: staging -> registers (tensor memory for its last SQT quads) ----
         mbar_wait(mbar, phase); phase ^= 1;
@@ -397,10 +410,10 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
         T4S(4);
         {
             const uint32_t next = prob + gridDim.x;
-            if (warp == 0 && next < a.batch) {
+            if (next < a.batch) {
                 issue_copy(a.Pinv + (size_t)next * a.mat_stride);
 #if TMEM4_L2_PREFETCH
-                if (lane == 0) l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
+                if (t == 32) l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
 #endif
             }
         }

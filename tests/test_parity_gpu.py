@@ -523,9 +523,10 @@ def test_symmetric_s_shipping(dt):
     it_s, ex_s = g.solve_batched_host(S_poison, None, gb, lam_s, nx, N, batch, sym)
     assert not ex_f.any() and not ex_s.any() and np.array_equal(it_f, it_s) and np.array_equal(lam_f, lam_s)
     check_against_oracle(S[0], P[0], gam[0], np.zeros(N * nx, dt), nx, N, tol, max_iter, lam_s[0], int(it_s[0]), False)
-    l1 = np.zeros(N * nx, dt)
+    l1, l2 = np.zeros(N * nx, dt), np.zeros(N * nx, dt)         # single-system host entry point: flag on poisoned S == no flag on S
     it1 = g.solvePCG(S_poison[1].copy(), gam[1], l1, nx, N, sym)
-    assert it1 == it_f[1] and np.array_equal(l1, lam_f[1])
+    it2 = g.solvePCG(Sb[1].copy(), gam[1], l2, nx, N, full)
+    assert it1 == it2 and np.array_equal(l1, l2)
 
 
 def test_fp64_batch_at_bench_size():
