@@ -155,6 +155,10 @@ __host__ __device__ inline Tmem4Plan make_tmem4_plan(int nx, int nxp, int N)
     return p;
 }
 constexpr int kTmem4MaxThreads = 128;    // 4 warps: one per tensor-memory lane quarter
+// Window stride per block-row (floats): exactly the four-row groups, 4 * ceil(nx/4).  (The register-row kernels pad 16-float blocks
+// to 20 for their 7-threads-per-block-row broadcast pattern; here that padding made the 16-byte publish stores of two neighbouring
+// block-rows collide -- 2x the wavefronts of every STS.128, 10 % of the kernel's shared-memory wavefronts, profiles/ncu_tmem4_r2d.txt.)
+__host__ __device__ constexpr int t4_nxp(int nx) { return 4 * ((nx + 3) / 4); }
 
 // ---- a thread's share of one matrix, quad by quad (compile-time recursion over the quad index) ----
 // the 4 rows x W columns of quad Q from the staged block-row image (column-major nx x 3nx panel); rowp = first row of this thread
@@ -297,7 +301,7 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     static_assert(NX % 2 == 0 && NX >= 4 && NX <= 16, "even state sizes up to 16");
     using T = float;
     using GEO = T4Geo<NX, SQT, PQR>;
-    constexpr int R = 4, G = GEO::G, NQT = GEO::NQT, BSZ = 3 * NX * NX, NXP = Geo<T>::nxp(NX);
+    constexpr int R = 4, G = GEO::G, NQT = GEO::NQT, BSZ = 3 * NX * NX, NXP = t4_nxp(NX);
     static_assert(GEO::cols <= 256, "a thread's tensor-memory columns (two CTAs share the SM's 512)");
     static_assert(NXP >= 4 * G, "a thread publishes four window entries");
 

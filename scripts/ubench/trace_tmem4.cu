@@ -43,7 +43,7 @@ int main(int argc, char **argv)
         cudaMemcpy(dg + b * vs, g.data(), vs * 4, cudaMemcpyHostToDevice);
     }
     auto kern = pcg_tmem4_kernel<NX, TR_SQT, TR_PQR>;
-    const Tmem4Plan plan = make_tmem4_plan(NX, Geo<float>::nxp(NX), N);
+    const Tmem4Plan plan = make_tmem4_plan(NX, t4_nxp(NX), N);
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     KernelArgs<float> a{};
