@@ -15,7 +15,7 @@
 #include "gbdpcg.h"
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
-#include "pcg_tmem8.cuh"
+#include "pcg_tmem4.cuh"
 #include "pcg_generic.cuh"
 #include "pcg_grid.cuh"
 #include "pcg_rows.cuh"
@@ -232,7 +232,6 @@ static size_t rows_smem(const RowsVariant *v, int bpc, int nbuf)
 
 const void *tmem_kernel_f32(int nx, const char **name);                                  // pcg_tmem_inst.cu
 const void *tmem4_kernel_f32(int nx, int variant, const char **name, int *alloc_cols);   // pcg_tmem_inst.cu
-const void *tmem8_kernel_f32(int nx, const char **name);                                 // pcg_tmem_inst.cu
 
 // Shared memory a tensor-memory CTA asks for: at least so much that the hardware cannot place more CTAs on an SM than
 // tensor memory has columns for (a surplus CTA would sit in tcgen05.alloc until a co-resident persistent CTA has
@@ -259,22 +258,6 @@ static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
         const int threads4 = round_up((int)(N * ((nx + 3) / 4)), 32);
         int variant = threads4 <= 64 ? 10 : 0, cols = 0;                                        // <= 2 warps: the <= 128-column variant, four CTAs per SM
         if (const char *e = getenv("GBDPCG_TMEM4_VARIANT")) variant = atoi(e);                  // tuning knob (A/B runs)
-        if (variant == 20) {
-            // experiment (GBDPCG_TMEM4_VARIANT=20): pcg_tmem8.cuh, the columns of a row group split between two lanes, 8 warps per system
-            const void *fn8 = tmem8_kernel_f32((int)nx, &name);
-            const int threads8 = round_up((int)(N * 2 * ((nx + 3) / 4)), 32);
-            if (fn8 && threads8 <= kTmem8MaxThreads) {
-                const size_t need = make_tmem8_plan((int)nx, t4_nxp((int)nx), (int)N).total;
-                const int per_sm = threads8 > 128 ? 2 : 4;
-                if ((size_t)per_sm * (need + 1024) <= 233472) {
-                    out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->tmem_per_sm = per_sm; out->v = nullptr;
-                    out->cluster = 1; out->bpc = (int)N; out->threads = threads8; out->nbuf = 1; out->pmode = P_REG;
-                    out->smem = tmem_smem_request(need, per_sm); out->fn = fn8; out->name = name; out->rpt = 4; out->fused = 1;
-                    return true;
-                }
-            }
-            return false;
-        }
         const void *fn4 = tmem4_kernel_f32((int)nx, variant, &name, &cols);
         if (fn4 && threads4 <= kTmem4MaxThreads) {
             int per_sm = 512 / cols;

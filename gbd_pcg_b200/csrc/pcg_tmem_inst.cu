@@ -1,6 +1,6 @@
 // pcg_tmem_inst.cu -- instantiations of the tensor-memory batched solvers, fp32, even state sizes <= 16:
 // pcg_tmem.cuh (two rows per thread, up to 8 warps per system) and pcg_tmem4.cuh (four rows per thread, up to 4 warps).
-#include "pcg_tmem8.cuh"
+#include "pcg_tmem4.cuh"
 
 namespace gbdpcg {
 
@@ -35,17 +35,6 @@ const void *tmem4_kernel_f32(int nx, int variant, const char **name, int *alloc_
     *name = nullptr;
     *alloc_cols = 0;
     return nullptr;
-}
-
-// Columns of a row group split between two lanes, 8 warps per system (pcg_tmem8.cuh): state sizes with an even number of quads per block.
-const void *tmem8_kernel_f32(int nx, const char **name)
-{
-    switch (nx) {
-    case 8: *name = "pcg_tmem8<f32,nx=8,R=4/2 lanes,S_tmem=0>"; return (const void *)pcg_tmem8_kernel<8, 0>;
-    case 14: *name = "pcg_tmem8<f32,nx=14,R=4/2 lanes,S_tmem=2>"; return (const void *)pcg_tmem8_kernel<14, 2>;
-    case 16: *name = "pcg_tmem8<f32,nx=16,R=4/2 lanes,S_tmem=2>"; return (const void *)pcg_tmem8_kernel<16, 2>;
-    default: *name = nullptr; return nullptr;
-    }
 }
 
 }  // namespace gbdpcg

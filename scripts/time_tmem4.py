@@ -21,7 +21,7 @@ nseed = 16
 SHAPES = {"c5": [(14, 7, 32)],
           "all": [(14, 7, 32), (12, 4, 40), (16, 8, 30), (16, 8, 32), (8, 4, 60), (10, 5, 17), (12, 6, 20), (14, 7, 16), (8, 4, 16)],
           "small": [(10, 5, 17), (8, 4, 30), (12, 6, 20), (14, 7, 16), (16, 8, 16), (8, 4, 16)]}[which]
-VARIANTS = {8: [0, 10, 20], 10: [0, 10], 12: [0, 1, 10], 14: [0, 1, 2, 3, 10, 20], 16: [0, 1, 20]}
+VARIANTS = {8: [0, 10], 10: [0, 10], 12: [0, 1, 10], 14: [0, 1, 2, 3, 10], 16: [0, 1]}
 
 
 def run(nx, N, d_S, d_P, d_g, flags, max_iter=1000, reps=11):
