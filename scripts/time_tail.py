@@ -15,7 +15,7 @@ nx, nu, N, nseed = 14, 7, 32, 64
 S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", np.float32)
 maxb = 8192
 d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(maxb // nseed, 1) for a in (S, P, gam))
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+flush = torch.zeros(64 << 20, dtype=torch.int32, device="cuda")      # 256 MB = 2 x L2, READ between launches (no dirty lines left behind)
 for batch in (148, 296, 444, 592, 740, 888, 1024, 1036, 1184, 2048, 4096, 8192):
     d_l = torch.zeros(batch, N * nx, dtype=torch.float32, device="cuda")
     d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
@@ -24,7 +24,7 @@ for batch in (148, 296, 444, 592, 740, 888, 1024, 1036, 1184, 2048, 4096, 8192):
     ts = []
     for i in range(25):
         d_l.zero_()
-        flush.zero_()
+        flush.sum()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, None)
