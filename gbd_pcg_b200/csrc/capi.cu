@@ -249,7 +249,7 @@ static size_t tmem_smem_request(size_t need, int per_sm)
 //                  <= 128 columns).  Taken when the system fits.
 //   pcg_tmem.cuh:  two rows per thread, <= 256 threads per system (GBDPCG_FLAG_TMEM_R2 forces it).
 // Worth it only when the batch fills every slot of the GPU.
-static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, uint32_t batch, Plan *out)
 {
     if (!has_p || (nx & 1u) || nx > 16 || N < 2 || cfg.cluster > 1) return false;
     if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_NO_TMA)) return false;
@@ -264,6 +264,16 @@ static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
             const int by_regs = 65536 / (256 * threads4);                                      // __launch_bounds__(128, 2): up to 255 registers
             if (by_regs < per_sm) per_sm = by_regs;
             const size_t need = make_tmem4_plan((int)nx, t4_nxp((int)nx), (int)N).total;
+            // Solo form: a launch of at most one system per SM (single solves, small batches) gives S a staging image of its own, so both
+            // matrices of a system are in flight at once and nothing of the next system arrives exposed (C2 single solve 22.6 us packed
+            // form against 26.7 for the register-row kernel, profiles/single_tmem4_r2f.txt).
+            const size_t solo = need + t4_stage_bytes((int)nx, (int)N);
+            if (threads4 >= 96 && batch <= (uint32_t)device_sms() && solo <= kMaxDynSmem && !getenv("GBDPCG_TMEM4_NO_SOLO")) {
+                out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->tmem_per_sm = 1; out->v = nullptr;
+                out->cluster = 1; out->bpc = (int)N; out->threads = threads4; out->nbuf = 2; out->pmode = P_REG;
+                out->smem = tmem_smem_request(solo, 1); out->fn = fn4; out->name = name; out->rpt = 4; out->fused = 1;
+                return true;
+            }
             // worth it with at least 8 warps on an SM (nx=12,N=20 at 2 x 2 warps: 0.48 ms against 0.40 for the two-row kernel; profiles/tmem4_r2a.txt)
             const bool enough_warps = per_sm * threads4 >= 256 || (cfg.flags & GBDPCG_FLAG_TMEM) || getenv("GBDPCG_TMEM4_VARIANT");
             if (enough_warps && (size_t)per_sm * (need + 1024) <= 233472) {
@@ -295,7 +305,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     int cnt;
     all_variants(f64, (int)nx, &tab, &cnt);
     if (cfg.flags & GBDPCG_FLAG_TMEM) {
-        if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, out)) return GBDPCG_OK; }
+        if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK; }
         return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 threads only (nx=%u N=%u %s)", nx, N,
                     f64 ? "f64" : "f32");
     }
@@ -306,11 +316,16 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
                                   GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_NO_TMA;
         // (two-row kernel: systems of <= 64 threads lose, the register-row kernel already fits four of them on an SM -- nx=8,N=16: 0.19 vs 0.21 ms)
+        // Four rows per thread, systems of 3-4 warps: every batch size -- above #SMs systems two CTAs per SM, up to #SMs the solo form
+        // (also the single solve).  Smaller systems and the two-row kernel: only when the batch fills every tensor-memory slot.
         Plan tp;
-        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_tmem(nx, N, has_p, cfg, &tp) &&
-            (unsigned long long)batch >= (unsigned long long)tp.tmem_per_sm * (unsigned long long)device_sms() && (tp.rpt == 4 || N * nx / 2 > 64)) {
-            *out = tp;
-            return GBDPCG_OK;
+        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_tmem(nx, N, has_p, cfg, batch, &tp)) {
+            const bool big4 = tp.rpt == 4 && tp.threads >= 96;
+            const bool fills = (unsigned long long)batch >= (unsigned long long)tp.tmem_per_sm * (unsigned long long)device_sms();
+            if (big4 || (fills && (tp.rpt == 4 || N * nx / 2 > 64))) {
+                *out = tp;
+                return GBDPCG_OK;
+            }
         }
     }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;

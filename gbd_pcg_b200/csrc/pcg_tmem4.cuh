@@ -138,6 +138,9 @@ __host__ __device__ constexpr bool t4_stage_alt(int nx) { return t4_stage_pad(nx
 // words from the start of the staging image to block-row lb
 __host__ __device__ constexpr int t4_stage_ofs(int nx, int lb) { return lb * 3 * nx * nx + (lb >> 1) * t4_stage_pad(nx); }
 
+// bytes of one staging image (+ slack for the gather's dropped reads)
+__host__ __device__ constexpr uint32_t t4_stage_bytes(int nx, int N) { return (uint32_t)((t4_stage_ofs(nx, N + 1) * 4 + 15) / 16 * 16 + 16); }
+
 struct Tmem4Plan {
     uint32_t mbar_off, tbase_off, red_off, winA_off, winB_off, stage_off, total;
 };
@@ -150,7 +153,7 @@ __host__ __device__ inline Tmem4Plan make_tmem4_plan(int nx, int nxp, int N)
     p.red_off = o;   o += 2 * 8 * 4;                                     // 2 slots x 4 warps x (gamma, delta)
     p.winA_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
     p.winB_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
-    p.stage_off = o; o += (uint32_t)round_up(t4_stage_ofs(nx, N + 1) * 4, 16) + 16;   // ONE matrix at a time (+ slack for the gather's dropped reads)
+    p.stage_off = o; o += t4_stage_bytes(nx, N);                         // ONE matrix at a time (a second image follows in the solo form)
     p.total = o;
     return p;
 }
@@ -314,6 +317,12 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     T *stage = reinterpret_cast<T *>(smem_raw + plan.stage_off);
     uint32_t *tbase_s = reinterpret_cast<uint32_t *>(smem_raw + plan.tbase_off);
     const uint32_t mbar = smem_u32(smem_raw + plan.mbar_off);
+    // Solo form (a.two_buffers: the launch has at most one CTA per SM -- single solves, batches of up to #SMs systems): S has a staging
+    // image and a barrier of its own behind the first, so both matrices of a system are in flight at once and the NEXT system's S is
+    // prefetched behind the iterations like its Phi^-1.  Packed form: S goes through the one image after Phi^-1 has left it.
+    const bool dual = a.two_buffers != 0;
+    T *stageS = dual ? reinterpret_cast<T *>(smem_raw + plan.stage_off + t4_stage_bytes(NX, N)) : stage;
+    const uint32_t mbarS = dual ? mbar + 8 : mbar;
 
     const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
     const int lb = t / G, g = t - lb * G;
@@ -323,7 +332,7 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
 
     for (int i = t; i < (N + 2) * NXP; i += blockDim.x) { winA[i] = 0.f; winB[i] = 0.f; }
     if (t < 16) red[t] = 0.f;
-    if (t == 0) { mbar_init(mbar, 1); fence_mbar_init(); }
+    if (t == 0) { mbar_init(mbar, 1); mbar_init(mbar + 8, 1); fence_mbar_init(); }
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(GEO::alloc_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
@@ -355,29 +364,34 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     const uint32_t mat_bytes = (uint32_t)(N * BSZ * (int)sizeof(T));
     // matrix image -> staging: one bulk copy (packed staging, thread 0), or one per pair of block-rows spread over the warps (padded
     // staging: a bulk copy is issued lane by lane, so the pairs are dealt to the warps first).  Called by every thread.
-    auto issue_copy = [&](const T *src) {
+    auto issue_copy = [&](const T *src, T *dst, const uint32_t bar) {
         if constexpr (t4_stage_pad(NX) == 0) {
             if (t == 0) {
                 fence_proxy_async();
-                mbar_expect_tx(mbar, mat_bytes);
-                bulk_g2s(smem_u32(stage), src, mat_bytes, mbar);
+                mbar_expect_tx(bar, mat_bytes);
+                bulk_g2s(smem_u32(dst), src, mat_bytes, bar);
             }
         } else {
             const int nwarps = (int)blockDim.x >> 5, npairs = (N + 1) >> 1;
             const int c = warp + nwarps * lane;                       // pair of block-rows this lane copies
-            if (t == 0) mbar_expect_tx(mbar, mat_bytes);
+            if (t == 0) mbar_expect_tx(bar, mat_bytes);
             if (c < npairs) {
                 fence_proxy_async();
                 const int rows = (2 * c + 2 <= N) ? 2 : 1;
-                bulk_g2s(smem_u32(stage + t4_stage_ofs(NX, 2 * c)), src + (size_t)(2 * c) * BSZ, (uint32_t)(rows * BSZ * sizeof(T)), mbar);
+                bulk_g2s(smem_u32(dst + t4_stage_ofs(NX, 2 * c)), src + (size_t)(2 * c) * BSZ, (uint32_t)(rows * BSZ * sizeof(T)), bar);
             }
         }
     };
-    uint32_t phase = 0;
-    if (blockIdx.x < a.batch) issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride);
+    // one barrier: Phi^-1 completes its even phases, S the odd ones; two barriers: each alternates on its own
+    uint32_t nP = 0, nS = 0;
+    if (blockIdx.x < a.batch) {
+        issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride, stage, mbar);
+        if (dual) issue_copy(a.S + (size_t)blockIdx.x * a.mat_stride, stageS, mbarS);
+    }
 
     const bool kill_left = !active || b == 0, kill_right = !active || b == N - 1, kill_mid = !active;
-    const T *rowp = stage + (active ? t4_stage_ofs(NX, lb) + 4 * g : 0);
+    const int rofs = active ? t4_stage_ofs(NX, lb) + 4 * g : 0;
+    const T *rowp = stage + rofs, *rowpS = stageS + rofs;
     const bool swap = t4_stage_alt(NX) && !(lb & 1);
 
     int sys_ord = -1;
@@ -398,27 +412,34 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
 
         // ---- Phi^-1: staging -> tensor memory (registers for its first PQR quads) ----
         T Pr[NQT][4][4], Sr[NQT][4][4];               // only the quads that stay in registers are ever touched
-        mbar_wait(mbar, phase); phase ^= 1;
+        mbar_wait(mbar, dual ? (nP & 1u) : 0u); ++nP;
         T4S(1);
         t4_load_matrix<GEO, NX, false, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Pr);
         __syncthreads();                                   // every thread has read its Phi^-1 rows: staging is free
         T4S(2);
-        issue_copy(a.S + (size_t)prob * a.mat_stride);
+        {
+            const uint32_t next = prob + gridDim.x;
+            if (!dual) issue_copy(a.S + (size_t)prob * a.mat_stride, stage, mbar);
+            else if (next < a.batch) issue_copy(a.Pinv + (size_t)next * a.mat_stride, stage, mbar);
+        }
 
         // ---- S: staging -> registers (tensor memory for its last SQT quads) ----
-        mbar_wait(mbar, phase); phase ^= 1;
+        mbar_wait(mbarS, dual ? (nS & 1u) : 1u); ++nS;
         T4S(3);
-        t4_load_matrix<GEO, NX, true, 0>(rowp, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Sr);
+        t4_load_matrix<GEO, NX, true, 0>(rowpS, hi_ok, swap, kill_left, kill_mid, kill_right, tmine, Sr);
         tmem_wait_st();
         __syncthreads();                                   // staging is free again: fetch the next system's Phi^-1 behind the iterations
         T4S(4);
         {
             const uint32_t next = prob + gridDim.x;
             if (next < a.batch) {
-                issue_copy(a.Pinv + (size_t)next * a.mat_stride);
+                if (dual) issue_copy(a.S + (size_t)next * a.mat_stride, stageS, mbarS);
+                else {
+                    issue_copy(a.Pinv + (size_t)next * a.mat_stride, stage, mbar);
 #if TMEM4_L2_PREFETCH
-                if (t == 32) l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
+                    if (t == 32) l2_prefetch_bulk(a.S + (size_t)next * a.mat_stride, mat_bytes);
 #endif
+                }
             }
         }
 

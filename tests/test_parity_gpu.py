@@ -758,7 +758,7 @@ def test_unaligned_device_pointers_fall_back_from_tma():
     """S / Phi^-1 at addresses that are only 4-byte aligned: the bulk-copy path must not be used, results unchanged."""
     torch = _torch()
     S, P, gam, nx, N, tol, max_iter = make_system("C2", "stair")
-    lam_a, it_a, _ = gpu_solve(S, P, gam, np.zeros(N * nx, np.float32), nx, N, tol, max_iter)
+    lam_a, it_a, _ = gpu_solve(S, P, gam, np.zeros(N * nx, np.float32), nx, N, tol, max_iter, flags=g._lib.FLAG_NO_TMEM)
     pad = lambda a: torch.from_numpy(np.concatenate([np.zeros(1, a.dtype), a])).cuda()[1:]
     d_S, d_P, d_g = pad(S), pad(P), pad(gam)
     assert d_S.data_ptr() % 16 == 4
@@ -854,7 +854,12 @@ def test_tmem_kernel_selection_and_refusals():
     cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0)
     assert "pcg_tmem" in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms)["kernel"]
     assert g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms)["max_resident"] == 2 * sms
-    assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, cfg, batch=2 * sms - 1)["kernel"]
+    # systems of 3-4 four-row warps take it at EVERY batch size: two CTAs per SM above #SMs systems, the solo form (one per SM, S with a
+    # staging image of its own) up to #SMs -- including the single solve
+    for b_, res in ((2 * sms - 1, 2 * sms), (sms + 1, 2 * sms), (sms, sms), (1, sms)):
+        info = g.plan_query(14, 32, np.float32, True, cfg, batch=b_)
+        assert "pcg_tmem4" in info["kernel"] and info["max_resident"] == res, (b_, info)
+    assert g.plan_query(14, 32, np.float32, True, cfg, batch=1)["smem_bytes"] > 2 * g.plan_query(14, 32, np.float32, True, cfg, batch=8192)["smem_bytes"] - 8192
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float64, True, cfg, batch=8192)["kernel"]
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, False, cfg, batch=8192)["kernel"]
     # the four-rows-per-thread kernel is the planner's choice where the system fits 128 such threads and an SM holds >= 8 warps of it
