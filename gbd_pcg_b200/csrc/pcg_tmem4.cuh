@@ -309,6 +309,9 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     static_assert(NXP >= 4 * G, "a thread publishes four window entries");
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
+#ifdef TMEM4_TRACE
+    if (threadIdx.x == 0 && blockIdx.x < 8) g_t4it[blockIdx.x][47][0] = clock64();      // kernel entry
+#endif
     const int N = (int)a.N;
     const Tmem4Plan plan = make_tmem4_plan(NX, NXP, N);
     T *red = reinterpret_cast<T *>(smem_raw + plan.red_off);
@@ -533,6 +536,9 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(GEO::alloc_cols) : "memory");
+#ifdef TMEM4_TRACE
+    if (threadIdx.x == 0 && blockIdx.x < 8) g_t4it[blockIdx.x][47][1] = clock64();      // kernel end
+#endif
 }
 
 }  // namespace gbdpcg

@@ -21,6 +21,7 @@ int main(int argc, char **argv)
 {
     const int NX = 14, N = 32, iters = argc > 1 ? atoi(argv[1]) : 25, batch = argc > 2 ? atoi(argv[2]) : 8192;
     const int grid = argc > 3 ? atoi(argv[3]) : 296;
+    const int solo = argc > 4 ? atoi(argv[4]) : 0;          // 1: the solo form (second staging image, at most one CTA per SM)
     const size_t ms = 3ull * N * NX * NX, vs = (size_t)N * NX;
     std::vector<float> S(ms, 0.f), P(ms, 0.f), g(vs);
     srand(1);
@@ -44,17 +45,18 @@ int main(int argc, char **argv)
     }
     auto kern = pcg_tmem4_kernel<NX, TR_SQT, TR_PQR>;
     const Tmem4Plan plan = make_tmem4_plan(NX, t4_nxp(NX), N);
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.total);
+    const size_t smem = plan.total + (solo ? t4_stage_bytes(NX, N) : 0);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     KernelArgs<float> a{};
     a.S = dS; a.Pinv = dP; a.gamma = dg; a.lambda = dl; a.iters = dit; a.exits = nullptr; a.mat_stride = ms; a.vec_stride = vs;
-    a.N = N; a.batch = batch; a.bpc = N; a.max_iter = iters; a.two_buffers = 0; a.use_tma = 1; a.tol = 0.f;
+    a.N = N; a.batch = batch; a.bpc = N; a.max_iter = iters; a.two_buffers = solo; a.use_tma = 1; a.tol = 0.f;
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float msec = 0, best = 1e9f;
     for (int rep = 0; rep < 10; rep++) {
         cudaMemset(dl, 0, vs * 4 * batch);
         cudaEventRecord(e0);
-        kern<<<grid, 128, plan.total>>>(a);
+        kern<<<grid, 128, smem>>>(a);
         cudaEventRecord(e1); cudaEventSynchronize(e1); cudaEventElapsedTime(&msec, e0, e1);
         if (msec < best) best = msec;
     }
@@ -66,6 +68,12 @@ int main(int argc, char **argv)
     cudaMemcpyFromSymbol(sy, g_t4sys, sizeof sy);
     cudaMemcpyFromSymbol(itr, g_t4it, sizeof itr);
     const int nsys = (batch + grid - 1) / grid < 40 ? (batch + grid - 1) / grid : 40;
+    {
+        const char *fn[] = {"wait Pinv", "Pinv->TMEM", "wait S", "S->regs", "prologue", "iterations", "outputs"};
+        printf("CTA 0, FIRST system, clocks from kernel entry: loop top +%lld;", sy[0][0][0] - itr[0][47][0]);
+        for (int m = 0; m < 7; m++) printf(" %s=%lld", fn[m], sy[0][0][m + 1] - sy[0][0][m]);
+        printf(" | kernel end +%lld after the outputs\n", itr[0][47][1] - sy[0][0][7]);
+    }
     const char *sn[] = {"wait Pinv", "Pinv->TMEM", "wait S", "S->regs", "prologue", "iterations", "outputs"};
     for (int c = 0; c < 2; c++) {
         double sum[7] = {0, 0, 0, 0, 0, 0, 0};
