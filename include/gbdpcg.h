@@ -77,7 +77,9 @@ typedef struct gbdpcg_config {
                                            tcgen05 GEMM on another stream) shares the SMs: tcgen05.alloc blocks until columns are free */
 #define GBDPCG_FLAG_TMEM_R2 0x1000u     /* with GBDPCG_FLAG_TMEM or the planner's own choice: the two-rows-per-thread tensor-memory kernel (pcg_tmem.cuh) even where the
                                            four-rows-per-thread one (pcg_tmem4.cuh, systems of up to 128 threads) applies -- A/B measurements */
-#define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick the tensor-memory kernel (the planner takes it for fp32 batches that fill its 2 or 4 slots per SM) */
+#define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick a tensor-memory kernel.  The planner takes one for fp32, Phi^-1 given, even nx <= 16, 16-byte aligned S / Phi^-1:
+                                           systems of 3-4 four-row warps (e.g. nx 14, 24 <= N <= 32) at every batch size including the single solve,
+                                           other shapes for batches that fill every tensor-memory slot of the GPU */
 #define GBDPCG_FLAG_SYMMETRIC_S 0x2000u /* host entry points (_solve_host, _solve_batched_host): the caller declares S symmetric (block (k, k-1) is the
                                            transpose of block (k-1, k), as PCG requires anyway): only the diagonal and right blocks are copied to the
                                            device -- 2/3 of the PCIe bytes -- and the left blocks are rebuilt there by transposition; whatever the
