@@ -54,7 +54,9 @@ SIGNATURES = {
     "gbdpcg_last_error": (C.c_char_p, []),
     "gbdpcg_last_cuda_error": (C.c_int, []),
     "gbdpcg_kernel_launches": (C.c_uint64, []),
+    "gbdpcg_solve_dev_static_scratch": (C.c_int, [C.c_int] + [_VP] * 4 + [_U32, _U32, _CFG, _VP, _VP, _VP]),
 }
+STATIC_SCRATCH_BYTES = 106496   # GBDPCG_STATIC_SCRATCH_BYTES
 for _s in ("f32", "f64"):
     SIGNATURES[f"gbdpcg_solve_host_{_s}"] = (C.c_int, [_VP] * 5 + [_U32, _U32, _CFG, C.POINTER(_U32), C.POINTER(_I32)])
     SIGNATURES[f"gbdpcg_solve_dev_{_s}"] = (C.c_int, [_VP] * 5 + [_U32, _U32, _CFG, _VP, _VP, _VP])

@@ -279,6 +279,19 @@ def solve_dev_async(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, con
                  _dev_ptr(d_iters, "d_iters", True), _dev_ptr(d_exit, "d_exit", True), _stream_ptr(stream)))
 
 
+def solve_dev_static_scratch(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, config, d_iters=None, d_exit=None, stream=None):
+    """``gbdpcg_solve_dev_static_scratch``: one solve on the cooperative-grid kernel with its exchange buffers in the library's
+    file-scope device array -- the call allocates nothing (no counterpart in the reference; include/gbdpcg.h).  Calls that
+    overlap on the GPU race on that array: keep them on one stream."""
+    cfg = config.to_c()
+    if d_Pinv is None:
+        cfg.empty_pinv = 1
+    _lib.check(_lib.lib().gbdpcg_solve_dev_static_scratch(
+        1 if _torch_dtype_suffix(d_S) == "f64" else 0, _dev_ptr(d_S, "d_S"), _dev_ptr(d_Pinv, "d_Pinv", True), _dev_ptr(d_gamma, "d_gamma"),
+        _dev_ptr(d_lambda, "d_lambda"), int(state_size), int(knot_points), C.byref(cfg), _dev_ptr(d_iters, "d_iters", True),
+        _dev_ptr(d_exit, "d_exit", True), _stream_ptr(stream)))
+
+
 def solve_batched_dev(state_size, knot_points, batch, d_S, d_Pinv, d_gamma, d_lambda, config, d_iters=None, d_exit=None,
                       stream=None):
     """Enqueue ``batch`` independent solves (problem-major slabs) on ``stream``."""

@@ -1127,6 +1127,89 @@ static int plan_query(uint32_t nx, uint32_t N, int has_pinv, uint32_t batch, con
 }  // namespace gbdpcg
 
 // ------------------------------------------------------------------------------------------------
+// allocation-free solve (gbdpcg_solve_dev_static_scratch): the cooperative-grid kernel with its exchange scratch in a
+// file-scope device array instead of the stream-ordered pool allocation of launch() above
+// ------------------------------------------------------------------------------------------------
+// Every GPU that loads the library holds these GBDPCG_STATIC_SCRATCH_BYTES until exit.  In host code the name below is only a
+// host-side stand-in for the symbol: the kernel gets the device address that cudaGetSymbolAddress returns (static_scratch_ptr).
+static __device__ __align__(256) unsigned char g_static_scratch[GBDPCG_STATIC_SCRATCH_BYTES];
+
+namespace gbdpcg {
+
+// device address of g_static_scratch on the CURRENT device; looked up once per device, with that device current
+static int static_scratch_ptr(void **out)
+{
+    constexpr int kMaxDev = 64;
+    static std::mutex mu;
+    static void *ptrs[kMaxDev] = {};
+    int dev;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDev) return fail(GBDPCG_ERR_UNSUPPORTED, "device ordinal %d is beyond the %d the static scratch table holds", dev, kMaxDev);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!ptrs[dev]) {
+        void *p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_static_scratch));
+        if (!p) return fail(GBDPCG_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch array");
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return GBDPCG_OK;
+}
+
+// One system on the cooperative-grid kernel (whatever its size: the planner's own path takes this kernel only beyond one cluster).
+// No cudaMalloc / cudaFree / pool allocation anywhere below; the kernel overwrites every scratch word before it reads it
+// (pcg_grid.cuh: each buffer is written between one pair of grid barriers and read between the next), so nothing has to be cleared.
+template <typename T>
+static int solve_dev_static_scratch(const T *S, const T *Pinv, const T *gamma, T *lambda, uint32_t nx, uint32_t N, const gbdpcg_config *cfg,
+                                    uint32_t *d_iters, uint8_t *d_exits, cudaStream_t stream)
+{
+    int rc = check_args(S, gamma, lambda, nx, N, cfg);
+    if (rc) return rc;
+    const bool has_p = use_pinv(Pinv, cfg);
+    Plan p;
+    if (!plan_grid<T>(nx, N, has_p, *cfg, &p))
+        return fail(GBDPCG_ERR_UNSUPPORTED, "no cooperative-grid kernel for nx=%u N=%u %s flags=0x%x cluster=%u (even nx <= 16, default recurrence, "
+                    "cluster = 0, N within the co-residency limit)", nx, N, sizeof(T) == 8 ? "f64" : "f32", cfg->flags, cfg->cluster);
+    const int G = p.cluster;
+    const size_t need = grid_scratch_elems<T>((int)nx, G) * sizeof(T);
+    if (need > (size_t)GBDPCG_STATIC_SCRATCH_BYTES)
+        return fail(GBDPCG_ERR_UNSUPPORTED, "nx=%u N=%u on %d CTAs needs %zu bytes of exchange scratch; the static array holds %d "
+                    "(GBDPCG_STATIC_SCRATCH_BYTES) -- use gbdpcg_solve_dev_*", nx, N, G, need, (int)GBDPCG_STATIC_SCRATCH_BYTES);
+    void *base = nullptr;
+    if ((rc = static_scratch_ptr(&base))) return rc;
+    if ((rc = prepare_fn(p.fn, false))) return rc;
+    int resident = 0;
+    if ((rc = max_resident_problems(p, &resident))) return rc;
+    if (resident < 1)
+        return fail(GBDPCG_ERR_UNSUPPORTED, "kernel %s cannot become resident (grid=%d threads=%d smem=%zu)", p.name, G, p.threads, p.smem);
+    KernelArgs<T> a;
+    a.S = S; a.Pinv = has_p ? Pinv : nullptr; a.gamma = gamma; a.lambda = lambda; a.iters = d_iters; a.exits = d_exits;
+    a.mat_stride = 3ull * N * nx * nx; a.vec_stride = (unsigned long long)N * nx;
+    a.N = N; a.batch = 1; a.bpc = (uint32_t)p.bpc; a.max_iter = cfg->max_iter; a.two_buffers = 0; a.use_tma = 0;
+    a.tol = (T)cfg->exit_tol;
+    T *scratch = reinterpret_cast<T *>(base);
+    GridScratch<T> gs;
+    gs.halo_r = scratch; gs.halo_rt = scratch + (size_t)G * 2 * nx; gs.halo_w = scratch + (size_t)G * 4 * nx;
+    gs.partials = scratch + (size_t)G * 6 * nx;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)G);
+    lc.blockDim = dim3(p.threads);
+    lc.dynamicSmemBytes = p.smem;
+    lc.stream = stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeCooperative;
+    at[0].val.cooperative = 1;
+    lc.attrs = at; lc.numAttrs = 1;
+    void *args[] = {&a, &gs};
+    const cudaError_t e = cudaLaunchKernelExC(&lc, p.fn, args);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaLaunchKernelExC (cooperative grid, static scratch)", __LINE__);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return GBDPCG_OK;
+}
+
+}  // namespace gbdpcg
+
+// ------------------------------------------------------------------------------------------------
 // extern "C"
 // ------------------------------------------------------------------------------------------------
 using namespace gbdpcg;
@@ -1203,6 +1286,16 @@ void gbdpcg_workspace_destroy(gbdpcg_workspace *ws)
 DEFINE_TYPED(f32, float)
 DEFINE_TYPED(f64, double)
 #undef DEFINE_TYPED
+
+int gbdpcg_solve_dev_static_scratch(int is_f64, const void *d_S, const void *d_Pinv, const void *d_gamma, void *d_lambda, uint32_t nx,
+                                    uint32_t N, const gbdpcg_config *cfg, uint32_t *d_iters, uint8_t *d_max_iter_exit, void *stream)
+{
+    if (is_f64)
+        return solve_dev_static_scratch<double>((const double *)d_S, (const double *)d_Pinv, (const double *)d_gamma, (double *)d_lambda, nx, N, cfg,
+                                                d_iters, d_max_iter_exit, (cudaStream_t)stream);
+    return solve_dev_static_scratch<float>((const float *)d_S, (const float *)d_Pinv, (const float *)d_gamma, (float *)d_lambda, nx, N, cfg, d_iters,
+                                           d_max_iter_exit, (cudaStream_t)stream);
+}
 
 int gbdpcg_plan_query(uint32_t nx, uint32_t N, int is_f64, int has_pinv, const gbdpcg_config *cfg, gbdpcg_plan_info *out)
 {

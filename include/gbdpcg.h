@@ -149,6 +149,26 @@ GBDPCG_API int gbdpcg_solve_batched_host_f64(gbdpcg_workspace *ws, const double 
                                   double *h_lambda, uint32_t nx, uint32_t N, uint32_t batch, const gbdpcg_config *cfg,
                                   uint32_t *h_iters, uint8_t *h_max_iter_exit);
 
+/* -- allocation-free device-pointer solve.  NO COUNTERPART IN THE REFERENCE: added for
+ *    callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *    One system on the cooperative-grid kernel (pcg_grid.cuh -- the kernel gbdpcg_solve_dev_* takes for systems beyond one 16-CTA
+ *    cluster, whose cross-CTA exchange buffers otherwise come from a stream-ordered pool allocation), with those buffers in a
+ *    file-scope device array of GBDPCG_STATIC_SCRATCH_BYTES that every GPU which loads the library holds until exit.  The call
+ *    makes no cudaMalloc / cudaFree / pool allocation.  Same arguments and semantics as gbdpcg_solve_dev_f32 / _f64 (is_f64
+ *    selects the element type of the four arrays); asynchronous on `stream`; d_iters / d_max_iter_exit may be NULL.
+ *    Limits: even nx <= 16, default recurrence (no GBDPCG_FLAG_TEXTBOOK), cfg->cluster == 0, N within the grid kernel's
+ *    co-residency limit, and  CTAs * (6*nx + 2) * sizeof(T) <= GBDPCG_STATIC_SCRATCH_BYTES, CTAs = the `cluster` field that
+ *    gbdpcg_plan_query reports for a grid-kernel shape (at most one per SM).  On a 148-SM B200 that admits every fp32 shape (at
+ *    most 58 KB), every fp64 shape up to nx = 14 (at most 101,824 B) and fp64 nx = 16 on up to 135 CTAs; GBDPCG_ERR_UNSUPPORTED
+ *    with a message naming both sizes otherwise (the caller then needs gbdpcg_solve_dev_*).
+ *    EVERY call on a device shares the one array (it keeps the last call's contents; the kernel overwrites each word before reading
+ *    it, so nothing is cleared): two calls that overlap on the GPU -- different streams, or different host threads -- RACE.
+ *    Serialise them on one stream, or use gbdpcg_solve_dev_* for concurrent solves. */
+#define GBDPCG_STATIC_SCRATCH_BYTES 106496 /* 104 KiB */
+GBDPCG_API int gbdpcg_solve_dev_static_scratch(int is_f64, const void *d_S, const void *d_Pinv, const void *d_gamma, void *d_lambda,
+                                               uint32_t nx, uint32_t N, const gbdpcg_config *cfg, uint32_t *d_iters,
+                                               uint8_t *d_max_iter_exit, void *stream);
+
 /* -- preconditioner construction on the device (no reference entry point: the reference
  *    carries glass::invertMatrix / glass::gemm / load_block_bd (GLASS/src/L3/inv.cuh:6-37, GLASS/src/L3/gemm.cuh:9-103,
  *    include/utils.cuh:96-161) for exactly this and never calls them).  From S in the compressed layout:
