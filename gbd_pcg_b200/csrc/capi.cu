@@ -180,6 +180,49 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
     return false;
 }
 
+// fp64 throughput form of the fused kernel (pcg_fused.cuh, PMODE = P_TMEM): two rows per thread, the rows of Phi^-1 and the last
+// columns of the rows of S in tensor memory -- a system needs half the SMs of the register-row plan (C3: a 2-CTA cluster of 224
+// threads instead of 4 CTAs).  The smallest cluster whose CTAs fit 256 threads, the shared-memory limit (staging holds one matrix
+// at a time) and 512 tensor-memory columns.
+template <typename T>
+static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+{
+    if constexpr (sizeof(T) != 8) {
+        return false;
+    } else {
+        if (!has_p) return false;
+        if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_NO_TMA | GBDPCG_FLAG_FORCE_GENERIC |
+                         GBDPCG_FLAG_LEGACY_ROWS))
+            return false;
+        const FusedVariant *tab = nullptr;
+        int cnt = 0, pair = 0, sk = 0;
+        if (const char *e = getenv("GBDPCG_TMEM64_VARIANT")) pair = atoi(e) ? 1 : 0;      // tuning knob (A/B runs)
+        switch (nx) {
+#define CASE(NX) case NX: tab = fused_tmem_variants_f64_##NX(&cnt); sk = fused_tmem_sk_f64_##NX(pair); break;
+            GBDPCG_FOR_EACH_NX_TMEM64(CASE)
+#undef CASE
+            default: break;
+        }
+        if (cnt < 2 * pair + 2) return false;
+        const int cpt = 2 * 2 * (3 * (int)nx + sk);                                       // tensor-memory columns per thread
+        static const int cl_opts[] = {1, 2, 4, 8, 16};
+        for (int cl : cl_opts) {
+            if (cfg.cluster && (int)cfg.cluster != cl) continue;
+            const int bpc = ((int)N + cl - 1) / cl;
+            const int threads = round_up(bpc * ((int)nx / 2), 32);
+            const FusedVariant *v = &tab[2 * pair + (cl > 1 ? 1 : 0)];
+            if (threads > v->maxt || ((threads + 127) / 128) * cpt > 512) continue;
+            const size_t smem = make_fused_plan<T>((int)nx, v->nxp, bpc, P_TMEM, 1).total;
+            if (smem > kMaxDynSmem) continue;
+            out->generic = false; out->fused_kernel = true; out->tmem_kernel = false; out->grid_kernel = false; out->v = nullptr;
+            out->cluster = cl; out->base_cluster = cl; out->bpc = bpc; out->threads = threads; out->nbuf = 1; out->pmode = P_TMEM;
+            out->smem = smem; out->fn = v->fn; out->name = v->name; out->rpt = 2; out->fused = 1;
+            return true;
+        }
+        return false;
+    }
+}
+
 // Systems too large for one 16-CTA cluster: a cooperative grid of register-row CTAs, at most one per SM (pcg_grid.cuh).
 // The reference runs any N whose N CTAs are co-resident (include/pcg.cuh:23-49); this covers N up to SMs x block-rows per CTA.
 template <typename T>
@@ -306,8 +349,9 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     all_variants(f64, (int)nx, &tab, &cnt);
     if (cfg.flags & GBDPCG_FLAG_TMEM) {
         if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK; }
-        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: fp32, Phi^-1 given, even nx <= 16 and N*nx/2 <= 256 threads only (nx=%u N=%u %s)", nx, N,
-                    f64 ? "f64" : "f32");
+        else { if (plan_fused_tmem64<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK; }
+        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: Phi^-1 given and fp32, even nx <= 16, N*nx/2 <= 256 threads -- or fp64, even nx 8..16, "
+                    "N*nx/2 <= 16 x 256 threads (nx=%u N=%u %s)", nx, N, f64 ? "f64" : "f32");
     }
     // Throughput mode: a batch that fills every tensor-memory slot of the GPU (two systems per SM above 128 threads per
     // system, four below) goes to the tensor-memory kernel -- same arithmetic bit for bit (C5: 1.18 -> 1.00 ms; nx=16,N=30:
@@ -323,6 +367,22 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
             const bool big4 = tp.rpt == 4 && tp.threads >= 96;
             const bool fills = (unsigned long long)batch >= (unsigned long long)tp.tmem_per_sm * (unsigned long long)device_sms();
             if (big4 || (fills && (tp.rpt == 4 || N * nx / 2 > 64))) {
+                *out = tp;
+                return GBDPCG_OK;
+            }
+        }
+    }
+    // fp64 throughput mode: a batch whose register-row clusters cannot all be resident at once takes the tensor-memory form of the
+    // fused kernel when that needs fewer SMs per system (C3 x 2048: 2-CTA clusters instead of 4-CTA ones)
+    if constexpr (f64) {
+        const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
+                                  GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_NO_TMA;
+        Plan tp, rp;
+        if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_fused_tmem64<T>(nx, N, has_p, cfg, &tp)) {
+            const bool have_reg = plan_fused<T>(nx, N, has_p, cfg, batch, &rp);
+            const bool throughput = (unsigned long long)batch * (unsigned long long)(have_reg ? rp.base_cluster : 1) > (unsigned long long)device_sms();
+            // (equal cluster sizes: still ahead where the register-row plan has to keep Phi^-1 in shared memory -- nx 16, N 32: 2.14 -> 1.29 ms)
+            if (have_reg && throughput && (tp.cluster < rp.base_cluster || (tp.cluster == rp.base_cluster && rp.pmode == P_SMEM))) {
                 *out = tp;
                 return GBDPCG_OK;
             }
@@ -562,6 +622,15 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
         const bool aligned = ((uintptr_t)S % 16 == 0) && (!P || (uintptr_t)P % 16 == 0) && ((a.mat_stride * sizeof(T)) % 16 == 0) &&
                              ((3ull * nx * nx * sizeof(T)) % 16 == 0);
         a.use_tma = (aligned && p.pmode != P_SMEM && !(cfg.flags & GBDPCG_FLAG_NO_TMA)) ? 1u : 0u;
+        if (p.pmode == P_TMEM && !a.use_tma) {
+            if (cfg.flags & GBDPCG_FLAG_TMEM) return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM needs 16-byte aligned S and Pinv");
+            // chosen by the planner: fall back to the register-row plan, which can stage with ordinary loads
+            gbdpcg_config c2 = cfg;
+            c2.flags |= GBDPCG_FLAG_NO_TMEM;
+            Plan p2;
+            if ((rc = make_plan<T>(nx, N, P != nullptr, c2, batch, &p2))) return rc;
+            return launch<T>(p2, S, P, gamma, lambda, nx, N, batch, c2, d_iters, d_exits, stream);
+        }
     }
     a.tol = (T)cfg.exit_tol;
 

@@ -58,6 +58,16 @@ GBDPCG_FOR_EACH_NX(GBDPCG_DECLARE_FUSED)
 GBDPCG_FOR_EACH_NX_EXTRA(GBDPCG_DECLARE_FUSED_EXTRA)
 #undef GBDPCG_DECLARE_FUSED_EXTRA
 
+// fp64 throughput form of the fused kernel (PMODE = P_TMEM, two rows per thread; pcg_fused_tmem_inst.cu): entries come in pairs
+// (one CTA, clustered) per choice of the S columns kept in tensor memory; fused_tmem_sk_f64_<nx>(pair) = that choice.
+// Keep in sync with NX_TMEM64 in the Makefile.
+#define GBDPCG_FOR_EACH_NX_TMEM64(X) X(8) X(10) X(12) X(14) X(16)
+#define GBDPCG_DECLARE_FTMEM(NX)                                   \
+    const FusedVariant *fused_tmem_variants_f64_##NX(int *count);  \
+    int fused_tmem_sk_f64_##NX(int pair);
+GBDPCG_FOR_EACH_NX_TMEM64(GBDPCG_DECLARE_FTMEM)
+#undef GBDPCG_DECLARE_FTMEM
+
 // Cooperative-grid kernel (pcg_grid.cuh): one table per (dtype, nx).
 struct GridVariant {
     int nx;

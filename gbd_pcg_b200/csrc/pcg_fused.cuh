@@ -34,6 +34,7 @@
 #include <stdint.h>
 
 #include "pcg_rows.cuh"  // KernelArgs, Geo, Vec16, abs_t, warp helpers, stage_block_rows, P_* enums
+#include "tmem_ops.cuh"  // tcgen05.ld / st wrappers (P_TMEM)
 
 #ifndef FUSED_NCH_R2
 #define FUSED_NCH_R2 2
@@ -75,7 +76,7 @@ namespace gbdpcg {
 // shared-memory plan (host sizes it, device carves it)
 // ---------------------------------------------------------------------------------------------
 struct FusedPlan {
-    uint32_t mbar_off, red_off, cred_off, winA_off, winB_off, stage_off, psm_off, ghost_off, xbar_off, total;
+    uint32_t mbar_off, red_off, cred_off, winA_off, winB_off, stage_off, psm_off, ghost_off, xbar_off, tbase_off, total;
 };
 // nstage: number of matrices the staging area holds side by side (2: S and Phi^-1 for P_REG; else 1)
 // PMODE == P_SMEM keeps Phi^-1 resident in its own area (psm) for the whole solve.
@@ -95,6 +96,7 @@ __host__ __device__ inline FusedPlan make_fused_plan(int nx, int nxp, int bpc, i
     // cluster-mode extras go last, so that the single-CTA layout (the batched hot path) is what it was measured with
     p.ghost_off = o; o += (uint32_t)round_up(8 * nxp * (int)sizeof(T), 16);   // ghost r [2 sides], s [2], w [2 parities][2 sides]
     p.xbar_off = o;  o += 32;                                                 // push mode: halo[2] and reduction[2] mbarriers
+    p.tbase_off = o; o += (pmode == P_TMEM) ? 16 : 0;                         // tensor-memory base address (tcgen05.alloc writes it)
     p.total = o;
     return p;
 }
@@ -389,6 +391,141 @@ __device__ __forceinline__ void block_row_mv(const T (&M)[R][3 * NX], const T *_
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// PMODE == P_TMEM (fp64 throughput mode).  The R rows of Phi^-1 a thread owns -- and the last SK panel columns of its rows
+// of S -- live in TENSOR MEMORY instead of registers, so a thread can own R = 2 fp64 rows (S alone would fill its 255
+// registers twice over together with Phi^-1) and a system needs half the SMs: C3 (nx 14, N 64, fp64, 602 KB of matrices)
+// runs on a 2-CTA cluster of 224 threads where the register-row plan needs 4 CTAs.
+// Layout, per thread (lane = the thread's lane, so the data is thread-private): panel column k of the block-row (k = j*NX + c,
+// j = left / diag / right block) takes R * (sizeof(T)/4) consecutive 32-bit columns, rows interleaved, so that one 16-column
+// tcgen05.ld delivers KPC consecutive panel columns of all R rows -- the operands of KPC/V 16-byte window loads.
+// Columns [0, PC): Phi^-1;  [PC, PC + SK*CPK): S, panel columns K0 .. 3NX-1.  Warps w and w+4 share a lane quarter and take
+// consecutive column ranges of CPT columns each.
+// ---------------------------------------------------------------------------------------------
+template <typename T, int NX, int R, int SK>
+struct TmGeo {
+    static constexpr int W32 = (int)sizeof(T) / 4;      // 32-bit columns per element
+    static constexpr int CPK = R * W32;                 // columns per panel column
+    static constexpr int KPC = 16 / CPK;                // panel columns per 16-column chunk
+    static constexpr int K0 = 3 * NX - SK;              // S: panel columns below K0 stay in registers
+    static constexpr int PC = 3 * NX * CPK;             // columns of Phi^-1
+    static constexpr int CPT = PC + SK * CPK;           // columns per thread
+    static_assert(16 % CPK == 0 && KPC >= 2, "a chunk holds whole panel columns");
+    static_assert(SK >= 0 && SK <= 3 * NX && SK % KPC == 0, "the S tail is whole chunks");
+};
+__host__ __device__ constexpr int tm_alloc_cols(int cpt, int threads)
+{
+    const int need = ((threads + 127) / 128) * cpt;     // warps per lane quarter x columns per thread
+    return need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
+}
+__device__ __forceinline__ uint32_t tm_lo(double x) { return (uint32_t)__double2loint(x); }
+__device__ __forceinline__ uint32_t tm_hi(double x) { return (uint32_t)__double2hiint(x); }
+
+// rows M[row][k], k in [KB, KE)  ->  tensor-memory columns from taddr on
+template <typename T, int NX, int R, int KB, int KE>
+__device__ __forceinline__ void tm_store_rows(const T (&M)[R][3 * NX], uint32_t taddr)
+{
+    static_assert(sizeof(T) == 8, "P_TMEM is the fp64 mode");
+    constexpr int CPK = R * 2, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC;
+    static_assert(REM == 0 || REM * CPK == 8, "the last chunk is whole or a half");
+#pragma unroll
+    for (int c = 0; c < NFULL; c++) {
+        uint32_t v[16];
+#pragma unroll
+        for (int kk = 0; kk < KPC; kk++)
+#pragma unroll
+            for (int row = 0; row < R; row++) {
+                v[(kk * R + row) * 2] = tm_lo(M[row][KB + c * KPC + kk]);
+                v[(kk * R + row) * 2 + 1] = tm_hi(M[row][KB + c * KPC + kk]);
+            }
+        tmem_st16(taddr + 16 * c, v);
+    }
+    if constexpr (REM != 0) {
+        uint32_t v[16];
+#pragma unroll
+        for (int kk = 0; kk < REM; kk++)
+#pragma unroll
+            for (int row = 0; row < R; row++) {
+                v[(kk * R + row) * 2] = tm_lo(M[row][KB + NFULL * KPC + kk]);
+                v[(kk * R + row) * 2 + 1] = tm_hi(M[row][KB + NFULL * KPC + kk]);
+            }
+        tmem_st8(taddr + 16 * NFULL, v);
+    }
+}
+
+// acc[row][k % NCH] += m(row, k) * x(k) for the panel columns k in [KB, KE) held in tensor memory from taddr on; `w` points at
+// the window slot of block b-1.  Chunks and their window pairs are double-buffered: chunk c+1 is in flight while c is multiplied.
+template <typename T, int NX, int R, int NCH, int KB, int KE>
+__device__ __forceinline__ void tm_mv_part(uint32_t taddr, const T *__restrict__ w, T (&acc)[R][NCH])
+{
+    static_assert(sizeof(T) == 8 && NX % 2 == 0 && KB % 2 == 0, "fp64, window pairs never straddle a block");
+    constexpr int NXP = Geo<T>::nxp(NX);
+    constexpr int CPK = R * 2, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC, NCHUNK = NFULL + (REM ? 1 : 0);
+    static_assert(KPC % 2 == 0 && REM % 2 == 0, "whole window pairs per chunk");
+    if constexpr (NCHUNK > 0) {
+        uint32_t u[2][16];
+        double2 x[2][KPC / 2];
+        auto issue = [&](int c, uint32_t (&dst)[16], double2 (&xd)[KPC / 2]) {
+            const int nk = (c < NFULL) ? KPC : REM;
+            if (nk == KPC) tmem_ld16(taddr + 16 * c, dst);
+            else tmem_ld8(taddr + 16 * c, dst);
+#pragma unroll
+            for (int h = 0; h < KPC / 2; h++) {
+                const int k = KB + c * KPC + 2 * h;
+                if (2 * h < nk) xd[h] = *reinterpret_cast<const double2 *>(w + (k / NX) * NXP + (k % NX));
+            }
+        };
+        issue(0, u[0], x[0]);
+#pragma unroll
+        for (int c = 0; c < NCHUNK; c++) {
+            const int nk = (c < NFULL) ? KPC : REM;
+            if (nk == KPC) tmem_wait_ld(u[c & 1]);
+            else tmem_wait_ld8(u[c & 1]);
+            if (c + 1 < NCHUNK) issue(c + 1, u[(c + 1) & 1], x[(c + 1) & 1]);
+#pragma unroll
+            for (int kk = 0; kk < KPC; kk++) {
+                if (kk < nk) {
+                    const int k = KB + c * KPC + kk;
+                    const double xv = (kk & 1) ? x[c & 1][kk / 2].y : x[c & 1][kk / 2].x;
+#pragma unroll
+                    for (int row = 0; row < R; row++) {
+                        const double m = __hiloint2double((int)u[c & 1][(kk * R + row) * 2 + 1], (int)u[c & 1][(kk * R + row) * 2]);
+                        acc[row][k % NCH] = __fma_rn(m, xv, acc[row][k % NCH]);
+                    }
+                }
+            }
+        }
+    }
+}
+
+// the same for the panel columns k in [0, KE) of a matrix whose rows are in registers
+template <typename T, int NX, int R, int NCH, int KE>
+__device__ __forceinline__ void tm_reg_part(const T (&M)[R][3 * NX], const T *__restrict__ w, T (&acc)[R][NCH])
+{
+    static_assert(sizeof(T) == 8 && NX % 2 == 0 && KE % 2 == 0, "fp64, window pairs never straddle a block");
+    constexpr int NXP = Geo<T>::nxp(NX);
+    constexpr int GRP = 8;                                  // panel columns whose window pairs are loaded together
+#pragma unroll
+    for (int g = 0; g < KE; g += GRP) {
+        double2 x[GRP / 2];
+#pragma unroll
+        for (int h = 0; h < GRP / 2; h++) {
+            const int k = g + 2 * h;
+            if (k < KE) x[h] = *reinterpret_cast<const double2 *>(w + (k / NX) * NXP + (k % NX));
+        }
+        asm volatile("" ::: "memory");
+#pragma unroll
+        for (int kk = 0; kk < GRP; kk++) {
+            const int k = g + kk;
+            if (k < KE) {
+                const double xv = (kk & 1) ? x[kk / 2].y : x[kk / 2].x;
+#pragma unroll
+                for (int row = 0; row < R; row++) acc[row][k % NCH] = __fma_rn(M[row][k], xv, acc[row][k % NCH]);
+            }
+        }
+    }
+}
+
 #ifdef GBDPCG_TRACE
 // phase timeline (scripts/ubench/trace_cluster.cu): clock64() of thread 0 of every CTA at the phase boundaries
 __device__ long long g_trace[16][64][8];
@@ -407,10 +544,14 @@ __device__ __forceinline__ double fma_t(double a, double b, double c) { return _
 // ---------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------
-template <typename T, int NX, int R, int PMODE, bool FUSED, bool CLUSTERED, int MAXT>
+template <typename T, int NX, int R, int PMODE, bool FUSED, bool CLUSTERED, int MAXT, int SK = 0>
 __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> a)
 {
     static_assert(NX % R == 0, "rows per thread must divide the state size");
+    constexpr bool TM = (PMODE == P_TMEM);                                      // Phi^-1 rows (and SK columns of S) in tensor memory
+    static_assert(!TM || (FUSED && sizeof(T) == 8 && MAXT <= 256), "P_TMEM: fp64, single-reduction recurrence, at most two warps per lane quarter");
+    static_assert(TM || SK == 0, "SK belongs to P_TMEM");
+    using TG = TmGeo<T, NX, R, TM ? SK : 0>;
     constexpr int NXP = Geo<T>::nxp(NX);
     constexpr int BSZ = 3 * NX * NX;
     constexpr int TPB = NX / R;                                                 // threads per block-row
@@ -474,6 +615,18 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         }
     }
 
+    // P_TMEM: warp 0 allocates the CTA's tensor-memory columns (a power of two that holds the warps of a lane quarter side by side)
+    uint32_t *tbase_s = reinterpret_cast<uint32_t *>(smem_raw + plan.tbase_off);
+    (void)tbase_s;
+    if constexpr (TM) {
+        if (warp == 0) {
+            const uint32_t ncols = (uint32_t)tm_alloc_cols(TG::CPT, (int)blockDim.x);
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(ncols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+
     // window B sits at the same offset from window A in every CTA, so one pair of remote pointers serves both
     const int wdelta = (int)((plan.winB_off - plan.winA_off) / sizeof(T));
     T *winA_prev = nullptr, *winA_next = nullptr, *ghost_w_prev = nullptr, *ghost_w_next = nullptr;
@@ -483,6 +636,13 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         if (rank + 1 < csize) { winA_next = cl.map_shared_rank(winA, rank + 1); ghost_w_next = cl.map_shared_rank(ghost_w, rank + 1); }
     }
     sync_all();
+    uint32_t tbase = 0, tmine = 0;
+    (void)tbase; (void)tmine;
+    if constexpr (TM) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        tbase = *tbase_s;
+        tmine = tbase + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * TG::CPT);
+    }
 
     const int slot = (lb + 1) * NXP + r0;                  // where this thread publishes its R vector elements
     const int wofs = (active ? lb : 0) * NXP;              // window [x_{b-1} | x_b | x_{b+1}] of this thread's block
@@ -572,9 +732,19 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             bulk_g2s(smem_u32(stageP), Pg, bytes, mbar);
         }
     };
+    // P_TMEM: the staging area holds ONE matrix at a time -- Phi^-1 (prefetched behind the previous system's iterations), then S
+    auto issue_one = [&](const T *M, uint32_t prob) {
+        const uint32_t bytes = (uint32_t)(nb * BSZ * (int)sizeof(T));
+        mbar_expect_tx(mbar, bytes);
+        bulk_g2s(smem_u32(stageS), M + (size_t)prob * a.mat_stride + (size_t)b0 * BSZ, bytes, mbar);
+    };
+    (void)issue_one;
     uint32_t phase = 0;
     XTRACE(1);
-    if (use_tma && t == 0 && nb > 0 && cluster_id < a.batch) issue_prefetch(cluster_id);
+    if (use_tma && t == 0 && nb > 0 && cluster_id < a.batch) {
+        if constexpr (TM) issue_one(a.Pinv, cluster_id);
+        else issue_prefetch(cluster_id);
+    }
 
     for (uint32_t prob = cluster_id; prob < a.batch; prob += n_clusters) {
         const size_t vofs = (size_t)prob * a.vec_stride + (size_t)b * NX + r0;
@@ -620,7 +790,15 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
 
         // Both paths end with the block-row images of S (and Phi^-1) in the staging area; the rows are then pulled
         // into registers from ONE place (two copies of that code overflow the register file).
-        if (use_tma) {
+        if constexpr (TM) {
+            // Phi^-1: staging -> tensor memory (through the registers S will occupy), then S through the same staging area
+            if (nb > 0) { mbar_wait(mbar, phase); phase ^= 1; }
+            load_rows(Sreg, stageS);
+            tm_store_rows<T, NX, R, 0, 3 * NX>(Sreg, tmine);
+            __syncthreads();                               // every thread has read its Phi^-1 rows: staging is free
+            if (t == 0 && nb > 0) { fence_proxy_async(); issue_one(a.S, prob); }
+            if (nb > 0) { mbar_wait(mbar, phase); phase ^= 1; }
+        } else if (use_tma) {
             if (nb > 0) { mbar_wait(mbar, phase); phase ^= 1; }
         } else {
             const T *Sg = a.S + (size_t)prob * a.mat_stride + (size_t)b0 * BSZ;
@@ -634,6 +812,10 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         XTRACE(2);
         load_rows(Sreg, stageS);
         if constexpr (PMODE == P_REG) load_rows(Preg, stageP);
+        if constexpr (TM) {
+            if constexpr (SK > 0) tm_store_rows<T, NX, R, TG::K0, 3 * NX>(Sreg, tmine + TG::PC);
+            tmem_wait_st();
+        }
         XTRACE(3);
         if constexpr (PMODE == P_SMEM) {
             // Phi^-1 stays in shared memory: clear its padding blocks in place (this CTA's first / last block-row)
@@ -645,15 +827,47 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
             // staging may be overwritten by the next system's matrices once every thread holds its rows
             __syncthreads();
             const uint32_t next = prob + n_clusters;
-            if (t == 0 && nb > 0 && next < a.batch && PMODE != P_SMEM) { fence_proxy_async(); issue_prefetch(next); }
+            if constexpr (TM) {
+                if (t == 0 && nb > 0 && next < a.batch) { fence_proxy_async(); issue_one(a.Pinv, next); }
+            } else {
+                if (t == 0 && nb > 0 && next < a.batch && PMODE != P_SMEM) { fence_proxy_async(); issue_prefetch(next); }
+            }
         } else if constexpr (PMODE == P_SMEM) {
             __syncthreads();
         }
         const T *Prow = psm + (active ? lb * BSZ + r0 : 0);
         (void)Prow;
 
+        // P_TMEM mat-vec: register part (S only), then the chunks in tensor memory; NCH chains per row, summed pairwise
+        auto mv_tm = [&](const bool is_S, const T *wp, T (&y)[R]) {
+            if constexpr (TM) {
+                constexpr int NCH = FUSED_NCH_F64;
+                T acc[R][NCH];
+#pragma unroll
+                for (int row = 0; row < R; row++)
+#pragma unroll
+                    for (int ch = 0; ch < NCH; ch++) acc[row][ch] = (T)0;
+                if (is_S) {
+                    tm_reg_part<T, NX, R, NCH, TG::K0>(Sreg, wp, acc);
+                    tm_mv_part<T, NX, R, NCH, TG::K0, 3 * NX>(tmine + TG::PC, wp, acc);
+                } else {
+                    tm_mv_part<T, NX, R, NCH, 0, 3 * NX>(tmine, wp, acc);
+                }
+#pragma unroll
+                for (int row = 0; row < R; row++) {
+#pragma unroll
+                    for (int n = NCH; n > 1; n = (n + 1) / 2) {
+#pragma unroll
+                        for (int i = 0; i < n / 2; i++) acc[row][i] = acc[row][i] + acc[row][i + (n + 1) / 2];
+                    }
+                    y[row] = acc[row][0];
+                }
+            }
+        };
+        (void)mv_tm;
         auto mv_S = [&](const T *win, T (&y)[R]) {
-            block_row_mv<T, NX, R, false>(Sreg, nullptr, win + wofs, y);
+            if constexpr (TM) mv_tm(true, win + wofs, y);
+            else block_row_mv<T, NX, R, false>(Sreg, nullptr, win + wofs, y);
             if (!active) {
 #pragma unroll
                 for (int i = 0; i < R; i++) y[i] = (T)0;
@@ -662,6 +876,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         auto mv_P = [&](const T *win, T (&y)[R]) {
             if constexpr (PMODE == P_REG) block_row_mv<T, NX, R, false>(Preg, nullptr, win + wofs, y);
             else if constexpr (PMODE == P_SMEM) block_row_mv<T, NX, R, true>(Sreg, Prow, win + wofs, y);
+            else if constexpr (TM) mv_tm(false, win + wofs, y);
             if (!active) {
 #pragma unroll
                 for (int i = 0; i < R; i++) y[i] = (T)0;
@@ -902,6 +1117,14 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         // the last reduction, and the partial-sum slots alternate.
     }
     if constexpr (CLUSTERED) cg::this_cluster().sync();   // no CTA may exit while a neighbour can still store into it
+    if constexpr (TM) {
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (warp == 0) {
+            const uint32_t ncols = (uint32_t)tm_alloc_cols(TG::CPT, (int)blockDim.x);
+            asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(ncols) : "memory");
+        }
+    }
     XTRACE(6);
 }
 

@@ -1,0 +1,49 @@
+// pcg_fused_tmem_inst.cu -- instantiates the fp64 throughput form of the fused kernel (pcg_fused.cuh, PMODE = P_TMEM): two rows
+// per thread, Phi^-1 rows and the last SK panel columns of the S rows in tensor memory.  Compiled once per state size with
+// -DINST_NX=<nx> (see csrc/Makefile).
+#include "kernel_table.h"
+#include "pcg_fused.cuh"
+
+#if !defined(INST_NX)
+#error "compile with -DINST_NX=<state size>"
+#endif
+
+namespace gbdpcg {
+
+#define CAT2_(a, b) a##b
+#define CAT2(a, b) CAT2_(a, b)
+#define STR_(x) #x
+#define STR(x) STR_(x)
+constexpr int NX = INST_NX;
+constexpr int MAXT = 256;      // 8 warps: two per tensor-memory lane quarter
+// Panel columns of S that go to tensor memory beside Phi^-1: what the register file cannot hold (2 rows x 3nx doubles of S are 12nx
+// registers; vectors, accumulators, window pairs and two tensor-memory chunks need about 130 more: nx 14 with 12 columns -> 250
+// registers, no spills; with 8 -> 255 and 48 bytes of spills; one chunk more measured equal or up to 4 % faster on every state
+// size, profiles/tmem64_r2k.txt).  A/B alternative in the second pair.
+#ifndef INST_SK_A
+#define INST_SK_A (((12 * INST_NX > 120) ? ((12 * INST_NX - 120 + 15) / 16 * 4) : 0) + 4)
+#endif
+#ifndef INST_SK_B
+#define INST_SK_B ((INST_SK_A) + 4)
+#endif
+constexpr int SK_A = INST_SK_A, SK_B = INST_SK_B;
+
+#define VARIANT(CL, SKV, SKNAME)                                                                              \
+    {NX, 1, 2, CL, P_TMEM, 1, MAXT, Geo<double>::nxp(NX),                                                       \
+     (const void *)pcg_fused_kernel<double, NX, 2, P_TMEM, true, (CL != 0), MAXT, SKV>,                       \
+     "pcg_fused<f64,nx=" STR(INST_NX) ",R=2," #CL ",P_TMEM,S_tmem=" SKNAME ">"}
+
+static const FusedVariant g_table[] = {
+    VARIANT(0, SK_A, "a"), VARIANT(1, SK_A, "a"),
+    VARIANT(0, SK_B, "b"), VARIANT(1, SK_B, "b"),
+};
+
+const FusedVariant *CAT2(fused_tmem_variants_f64_, INST_NX)(int *count)
+{
+    *count = (int)(sizeof g_table / sizeof g_table[0]);
+    return g_table;
+}
+// columns of S in tensor memory of entry pair 0 / 1 (the planner sizes the allocation check with it)
+int CAT2(fused_tmem_sk_f64_, INST_NX)(int pair) { return pair == 0 ? SK_A : SK_B; }
+
+}  // namespace gbdpcg

@@ -27,7 +27,7 @@
 namespace gbdpcg {
 namespace cg = cooperative_groups;
 
-enum : int { P_NONE = 0, P_REG = 1, P_SMEM = 2 };
+enum : int { P_NONE = 0, P_REG = 1, P_SMEM = 2, P_TMEM = 4 };   // (3 = global memory, the run-time-nx kernel's plan report)
 
 template <typename T>
 struct KernelArgs {

@@ -73,8 +73,11 @@ typedef struct gbdpcg_config {
  * PRECONDITIONED solve, and it halves the bytes a host-resident batch has to push over PCIe. */
 #define GBDPCG_FLAG_TMEM 0x400u         /* fp32 batched: two (small systems: four) systems per SM with Phi^-1 in tensor memory (pcg_tmem4.cuh: four rows per
                                            thread, S in registers; pcg_tmem.cuh: two rows per thread for systems of more than 128 such threads);
-                                           GBDPCG_ERR_UNSUPPORTED for shapes neither covers.  Assumes no other tensor-memory user (e.g. a concurrent
-                                           tcgen05 GEMM on another stream) shares the SMs: tcgen05.alloc blocks until columns are free */
+                                           GBDPCG_ERR_UNSUPPORTED for shapes neither covers.  fp64 (even nx 8..16): the tensor-memory form of the cluster
+                                           kernel (pcg_fused.cuh, P_TMEM: two rows per thread, Phi^-1 rows in tensor memory, half the SMs per system) --
+                                           what the planner itself takes for fp64 batches too large to be resident at once.  Assumes no other
+                                           tensor-memory user (e.g. a concurrent tcgen05 GEMM on another stream) shares the SMs: tcgen05.alloc blocks
+                                           until columns are free */
 #define GBDPCG_FLAG_TMEM_R2 0x1000u     /* with GBDPCG_FLAG_TMEM or the planner's own choice: the two-rows-per-thread tensor-memory kernel (pcg_tmem.cuh) even where the
                                            four-rows-per-thread one (pcg_tmem4.cuh, systems of up to 128 threads) applies -- A/B measurements */
 #define GBDPCG_FLAG_NO_TMEM 0x800u      /* never pick a tensor-memory kernel.  The planner takes one for fp32, Phi^-1 given, even nx <= 16, 16-byte aligned S / Phi^-1:
@@ -246,7 +249,7 @@ typedef struct gbdpcg_plan_info {
     int32_t cluster;       /* CTAs per problem                                                   */
     int32_t threads;       /* threads per CTA                                                    */
     int32_t block_rows;    /* block-rows (knot points) owned by one CTA                          */
-    int32_t pinv_mode;     /* 0 identity, 1 registers, 2 shared memory, 3 global (fallback)      */
+    int32_t pinv_mode;     /* 0 identity, 1 registers, 2 shared memory, 3 global (fallback), 4 tensor memory (fp64 throughput form) */
     int32_t regs;          /* registers per thread of the chosen kernel                          */
     uint64_t smem_bytes;   /* dynamic shared memory per CTA                                      */
     int32_t max_resident;  /* problems resident at once on the current device                    */

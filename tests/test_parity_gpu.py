@@ -848,7 +848,7 @@ def test_tmem_kernel_edge_semantics(arm):
 
 def test_tmem_kernel_selection_and_refusals():
     """The planner takes the tensor-memory kernel for fp32 batches that fill the GPU twice; it is refused (flag forced) or
-    avoided (planner) for fp64, identity preconditioner, odd / large state sizes and unaligned pointers."""
+    avoided (planner) for the identity preconditioner, odd / large state sizes and unaligned pointers."""
     torch = _torch()
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, empty_pinv=0)
@@ -872,7 +872,9 @@ def test_tmem_kernel_selection_and_refusals():
     assert "pcg_tmem" not in g.plan_query(10, 17, np.float32, True, cfg, batch=4 * sms - 1)["kernel"]
     assert "pcg_tmem" not in g.plan_query(8, 16, np.float32, True, cfg, batch=8192)["kernel"]       # one warp per system: the register-row kernel wins
     assert "pcg_tmem" not in g.plan_query(14, 32, np.float32, True, g.pcg_config(flags=g._lib.FLAG_NO_TMEM), batch=8192)["kernel"]
-    for (nx, N, dt, has_p) in [(14, 32, np.float64, True), (14, 32, np.float32, False), (15, 20, np.float32, True), (18, 20, np.float32, True),
+    # (fp64 + GBDPCG_FLAG_TMEM is the tensor-memory form of the cluster kernel: tests/test_tmem64_gpu.py)
+    assert "P_TMEM" in g.plan_query(14, 32, np.float64, True, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=8192)["kernel"]
+    for (nx, N, dt, has_p) in [(14, 32, np.float64, False), (14, 32, np.float32, False), (15, 20, np.float32, True), (18, 20, np.float32, True),
                                (14, 40, np.float32, True)]:
         with pytest.raises(g.GbdpcgError):
             g.plan_query(nx, N, dt, has_p, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=8192)
