@@ -1,5 +1,5 @@
 """Small driver for ncu captures: a few launches of the batched kernel (C5) and of the single-system kernels (C2, C3, C4).
-usage: python scripts/prof_kernel.py [batched|single|all] [batch]"""
+usage: python scripts/prof_kernel.py [batched|batched64|single|all] [batch]"""
 import os
 import sys
 
@@ -25,6 +25,19 @@ if what in ("batched", "all"):
         g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, None)
     torch.cuda.synchronize()
     print("batched iters", d_it.float().mean().item())
+
+if what == "batched64":      # fp64 throughput form (P_TMEM): C3 systems
+    nx, nu, N = 14, 7, 64
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(32), "stair", np.float64)
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // 32, 1) for a in (S, P, gam))
+    d_l = torch.zeros(batch, N * nx, dtype=torch.float64, device="cuda")
+    d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
+    cfg = g.pcg_config(pcg_exit_tol=1e-10, pcg_max_iter=2000, empty_pinv=0, flags=int(os.environ.get("PROF_FLAGS", "0"), 0))
+    for _ in range(3):
+        d_l.zero_()
+        g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, d_l, cfg, d_it, None)
+    torch.cuda.synchronize()
+    print("batched64 iters", d_it.float().mean().item(), g.plan_query(nx, N, np.float64, True, cfg, batch=batch)["kernel"])
 
 if what in ("single", "all"):
     for name in ("C2", "C3", "C4"):
