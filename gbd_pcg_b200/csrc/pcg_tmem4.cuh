@@ -370,6 +370,11 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     if (blockIdx.x < a.batch) {
         issue_copy(a.Pinv + (size_t)blockIdx.x * a.mat_stride, stage, mbar);
         if (dual) issue_copy(a.S + (size_t)blockIdx.x * a.mat_stride, stageS, mbarS);
+#if TMEM4_L2_PREFETCH
+        // packed form: the first system's S follows its Phi^-1 through the one staging image; start its HBM read now, so that the two
+        // cold reads of a launch's first wave overlap instead of queueing (first-system "wait S" 3283 -> L2-hit time)
+        else if (t == 32) l2_prefetch_bulk(a.S + (size_t)blockIdx.x * a.mat_stride, mat_bytes);
+#endif
     }
 
     const bool kill_left = !active || b == 0, kill_right = !active || b == N - 1, kill_mid = !active;

@@ -61,5 +61,6 @@ for case in range(ncase):
     worst = [max(e[j] for e in errs) for j in range(4)]
     fail = worst[0] > bar or worst[1] > bar or worst[2] > bar * 2 or worst[3] > (5e-3 if dt == np.float32 else 1e-6) or not all(e[4] for e in errs) or not same or int(ex.sum().item()) != 0
     bad += fail
-    print(f"case {case:3d}: nx={nx:2d} nu={nu:2d} N={N:3d} B={B:3d} {np.dtype(dt).name:7s} {kind:6s} S {worst[0]:.1e} gamma {worst[1]:.1e} Pinv {worst[2]:.1e} lambda {worst[3]:.1e} iters {[(e[5], e[6]) for e in errs]} same={same} {'FAIL' if fail else 'ok'}", flush=True)
+    kern = g.plan_query(nx, N, dt, True, g.pcg_config(empty_pinv=0), batch=B)["kernel"].split("<")[0] + ("/P_TMEM" if "P_TMEM" in g.plan_query(nx, N, dt, True, g.pcg_config(empty_pinv=0), batch=B)["kernel"] else "")
+    print(f"case {case:3d}: nx={nx:2d} nu={nu:2d} N={N:3d} B={B:3d} {np.dtype(dt).name:7s} {kind:6s} {kern:18s} S {worst[0]:.1e} gamma {worst[1]:.1e} Pinv {worst[2]:.1e} lambda {worst[3]:.1e} iters {[(e[5], e[6]) for e in errs]} same={same} {'FAIL' if fail else 'ok'}", flush=True)
 print("FAILED" if bad else "ALL OK", bad)
