@@ -291,6 +291,7 @@ static size_t tmem_smem_request(size_t need, int per_sm)
 //   pcg_tmem4.cuh: four rows per thread, <= 128 threads per system, two CTAs per SM (four when a CTA has <= 2 warps and
 //                  <= 128 columns).  Taken when the system fits.
 //   pcg_tmem.cuh:  two rows per thread, <= 256 threads per system (GBDPCG_FLAG_TMEM_R2 forces it).
+//   pcg_tmem4.cuh, wide form: four rows per thread, 129..256 threads per system (nx 14: 37 <= N <= 64), one CTA per SM.
 // Worth it only when the batch fills every slot of the GPU.
 static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, uint32_t batch, Plan *out)
 {
@@ -330,7 +331,18 @@ static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
     const void *fn = tmem_kernel_f32((int)nx, &name);
     if (!fn) return false;
     const int threads = round_up((int)(N * nx / 2), 32);
-    if (threads > kTmemMaxThreads) return false;
+    if (threads > kTmemMaxThreads) {
+        // beyond the two-row kernel: the WIDE four-row form, 8 warps (two per lane quarter), one CTA per SM (nx 14: N <= 64)
+        const int threads4 = round_up((int)(N * ((nx + 3) / 4)), 32);
+        int cols = 0;
+        const void *fnw = (cfg.flags & GBDPCG_FLAG_TMEM_R2) ? nullptr : tmem4_kernel_f32((int)nx, 20, &name, &cols);
+        const size_t need = make_tmem4_plan((int)nx, t4_nxp((int)nx), (int)N).total;
+        if (!fnw || threads4 > kTmem4WideThreads || need > kMaxDynSmem) return false;
+        out->generic = false; out->fused_kernel = false; out->tmem_kernel = true; out->tmem_per_sm = 1; out->v = nullptr; out->cluster = 1;
+        out->bpc = (int)N; out->threads = threads4; out->nbuf = 1; out->pmode = P_REG; out->smem = tmem_smem_request(need, 1); out->fn = fnw;
+        out->name = name; out->rpt = 4; out->fused = 1;
+        return true;
+    }
     const size_t smem = make_tmem_plan((int)nx, Geo<float>::nxp((int)nx), (int)N).total;
     const int per_sm = 512 / tmem_cols(threads);
     if ((size_t)per_sm * (smem + 1024) > 233472) return false;   // as many CTAs per SM as tensor memory allows, or it is pointless
@@ -350,7 +362,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     if (cfg.flags & GBDPCG_FLAG_TMEM) {
         if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK; }
         else { if (plan_fused_tmem64<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK; }
-        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: Phi^-1 given and fp32, even nx <= 16, N*nx/2 <= 256 threads -- or fp64, even nx 8..16, "
+        return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: Phi^-1 given and fp32, even nx <= 16, N*ceil(nx/4) <= 256 threads -- or fp64, even nx 8..16, "
                     "N*nx/2 <= 16 x 256 threads (nx=%u N=%u %s)", nx, N, f64 ? "f64" : "f32");
     }
     // Throughput mode: a batch that fills every tensor-memory slot of the GPU (two systems per SM above 128 threads per
@@ -364,9 +376,17 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         // (also the single solve).  Smaller systems and the two-row kernel: only when the batch fills every tensor-memory slot.
         Plan tp;
         if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_tmem(nx, N, has_p, cfg, batch, &tp)) {
-            const bool big4 = tp.rpt == 4 && tp.threads >= 96;
+            const bool wide = tp.rpt == 4 && tp.threads > kTmem4MaxThreads;
+            const bool big4 = tp.rpt == 4 && tp.threads >= 96 && !wide;
             const bool fills = (unsigned long long)batch >= (unsigned long long)tp.tmem_per_sm * (unsigned long long)device_sms();
-            if (big4 || (fills && (tp.rpt == 4 || N * nx / 2 > 64))) {
+            // the wide form (one system per SM) replaces register-row CLUSTERS in throughput mode only: a batch that cannot be resident at once
+            bool wide_wins = false;
+            if (wide) {
+                Plan rp;
+                wide_wins = plan_fused<T>(nx, N, has_p, cfg, batch, &rp) && rp.base_cluster > 1 &&
+                            (unsigned long long)batch * (unsigned long long)rp.base_cluster > (unsigned long long)device_sms();
+            }
+            if (big4 || wide_wins || (!wide && fills && (tp.rpt == 4 || N * nx / 2 > 64))) {
                 *out = tp;
                 return GBDPCG_OK;
             }

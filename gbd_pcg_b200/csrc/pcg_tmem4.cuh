@@ -130,14 +130,15 @@ __host__ __device__ inline Tmem4Plan make_tmem4_plan(int nx, int nxp, int N)
     uint32_t o = 0;
     p.mbar_off = o;  o += 16;
     p.tbase_off = o; o += 16;
-    p.red_off = o;   o += 2 * 8 * 4;                                     // 2 slots x 4 warps x (gamma, delta)
+    p.red_off = o;   o += 2 * 16 * 4;                                    // 2 slots x up to 8 warps x (gamma, delta)
     p.winA_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
     p.winB_off = o;  o += (uint32_t)round_up((N + 2) * nxp * 4, 16);
     p.stage_off = o; o += t4_stage_bytes(nx, N);                         // ONE matrix at a time (a second image follows in the solo form)
     p.total = o;
     return p;
 }
-constexpr int kTmem4MaxThreads = 128;    // 4 warps: one per tensor-memory lane quarter
+constexpr int kTmem4MaxThreads = 128;    // 4 warps: one per tensor-memory lane quarter (two such CTAs per SM)
+constexpr int kTmem4WideThreads = 256;   // wide form: 8 warps, two per lane quarter side by side in the columns, one CTA per SM
 // Window stride per block-row (floats): exactly the four-row groups, 4 * ceil(nx/4).  (The register-row kernels pad 16-float blocks
 // to 20 for their 7-threads-per-block-row broadcast pattern; here that padding made the 16-byte publish stores of two neighbouring
 // block-rows collide -- 2x the wavefronts of every STS.128, 10 % of the kernel's shared-memory wavefronts, profiles/ncu_tmem4_r2d.txt.)
@@ -278,12 +279,18 @@ __device__ __forceinline__ void t4_mv_step(const float (&Mr)[GEO::NQT][4][4], co
     }
 }
 
-template <int NX, int SQT, int PQR>
-__global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const KernelArgs<float> a)
+// NWQ = warps per tensor-memory lane quarter: 1 -> systems of up to 128 four-row threads, two CTAs per SM (the C5 kernel);
+// 2 -> the WIDE form, up to 256 threads (nx 14: N <= 64), one CTA per SM: warps w and w+4 keep their columns side by side.
+template <int NX, int SQT, int PQR, int NWQ = 1>
+__global__ void __launch_bounds__(128 * NWQ, NWQ == 1 ? 2 : 1) pcg_tmem4_kernel(const KernelArgs<float> a)
 {
     static_assert(NX % 2 == 0 && NX >= 4 && NX <= 16, "even state sizes up to 16");
+    static_assert(NWQ == 1 || NWQ == 2, "one or two warps per lane quarter");
     using T = float;
     using GEO = T4Geo<NX, SQT, PQR>;
+    constexpr int NW = 4 * NWQ;                                                   // warps whose partials a reduction sums
+    constexpr int ALLOC = NWQ == 1 ? GEO::alloc_cols : (2 * GEO::cols <= 64 ? 64 : 2 * GEO::cols <= 128 ? 128 : 2 * GEO::cols <= 256 ? 256 : 512);
+    static_assert(NWQ * GEO::cols <= 512, "the warps of a lane quarter share its 512 columns");
     constexpr int R = 4, G = GEO::G, NQT = GEO::NQT, BSZ = 3 * NX * NX, NXP = t4_nxp(NX);
     static_assert(GEO::cols <= 256, "a thread's tensor-memory columns (two CTAs share the SM's 512)");
     static_assert(NXP >= 4 * G, "a thread publishes four window entries");
@@ -314,17 +321,17 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
     const int b = lb;
 
     for (int i = t; i < (N + 2) * NXP; i += blockDim.x) { winA[i] = 0.f; winB[i] = 0.f; }
-    if (t < 16) red[t] = 0.f;
+    if (t < 4 * NW) red[t] = 0.f;
     if (t == 0) { mbar_init(mbar, 1); mbar_init(mbar + 8, 1); fence_mbar_init(); }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(GEO::alloc_cols) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(ALLOC) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tbase = *tbase_s;
-    const uint32_t tmine = tbase + ((uint32_t)(32 * warp) << 16);
+    const uint32_t tmine = tbase + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * GEO::cols);
 
     const int slot = (lb + 1) * NXP + 4 * g;
     const int wofs = (active ? lb : 0) * NXP;
@@ -336,10 +343,10 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
         Pair<T> p(x0, x1);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) p = p + shfl_xor_pair<T>(p, o);
-        T *rd = red + red_slot * 8;
+        T *rd = red + red_slot * 2 * NW;
         if (lane == 0) *reinterpret_cast<float2 *>(rd + 2 * warp) = make_float2(p.x(), p.y());
         __syncthreads();
-        Pair<T> s = pair_tree_sum<T, 4>(rd);
+        Pair<T> s = pair_tree_sum<T, NW>(rd);
         red_slot ^= 1;
         return s;
     };
@@ -520,7 +527,7 @@ __global__ void __launch_bounds__(kTmem4MaxThreads, 2) pcg_tmem4_kernel(const Ke
 
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(GEO::alloc_cols) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(ALLOC) : "memory");
 #ifdef TMEM4_TRACE
     if (threadIdx.x == 0 && blockIdx.x < 8) g_t4it[blockIdx.x][47][1] = clock64();      // kernel end
 #endif

@@ -32,6 +32,15 @@ const void *tmem4_kernel_f32(int nx, int variant, const char **name, int *alloc_
     V(14, 0, 2, 0) V(14, 1, 4, 0) V(14, 2, 6, 6) V(14, 3, 0, 0) V(14, 10, 0, 3)
     V(16, 0, 6, 2) V(16, 1, 4, 0)
 #undef V
+    // id 20: the wide form (8 warps, two per lane quarter, one CTA per SM) for systems of 129..256 four-row threads
+#define W(NX, SQT, PQR)                                                                     \
+    if (nx == NX && variant == 20) {                                                        \
+        *name = "pcg_tmem4<f32,nx=" #NX ",R=4,S_tmem=" #SQT ",P_reg=" #PQR ",wide,1 per SM>"; \
+        *alloc_cols = 512;                                                                  \
+        return (const void *)pcg_tmem4_kernel<NX, SQT, PQR, 2>;                             \
+    }
+    W(8, 0, 0) W(10, 0, 0) W(12, 3, 3) W(14, 2, 0) W(16, 6, 2)
+#undef W
     *name = nullptr;
     *alloc_cols = 0;
     return nullptr;
