@@ -551,6 +551,42 @@ def single_gpu_extras(torch, g, _lib, S, P, gam, cfg, cfg_build, d_S, d_P, d_it,
                            "hbm_line_solves_per_s": peak * 1e9 / b64, "kernel": p64["kernel"], "cluster": p64["cluster"], "threads": p64["threads"],
                            "parity_max_rel_err_vs_oracle": worst}
     del dS, dP, dg, dl, di
+
+    # ---- fp32 batch of systems twice the knot points of C2: 4096 x (nx 14, N 64, fp32, tol 1e-6, stair) -- the wide form of the four-row
+    #      tensor-memory kernel (8 warps, one system per SM) where the register-row plan needs a 2-CTA cluster per system ----
+    wnx, wnu, wN, wtol, wmax = 14, 7, 64, 1e-6, 1000
+    nbw, nseedw = 4096, 64
+    Sw, Pw, gw = g.synth.lqr_schur_batch(wnx, wnu, wN, range(nseedw), "stair", np.float32)
+    dS, dP, dg = (torch.from_numpy(a).cuda().repeat(nbw // nseedw, 1) for a in (Sw, Pw, gw))
+    dl = torch.zeros(nbw, wN * wnx, dtype=torch.float32, device="cuda")
+    di = torch.zeros(nbw, dtype=torch.int32, device="cuda")
+    wcfg = g.pcg_config(pcg_exit_tol=wtol, pcg_max_iter=wmax, empty_pinv=0)
+
+    def stepw():
+        g.solve_batched_dev(wnx, wN, nbw, dS, dP, dg, dl, wcfg, di, None)
+    for _ in range(3):
+        dl.zero_()
+        stepw()
+    sync()
+    ev = timed_launches(torch, stepw, dl.zero_, 10)
+    sync()
+    msw = st.mean(a.elapsed_time(b) for a, b in ev)
+    bw = layout.algorithmic_bytes(wnx, wN, 4, True)
+    pw = g.plan_query(wnx, wN, np.float32, True, wcfg, batch=nbw)
+    worst = 0.0
+    itsw = di.cpu().numpy()
+    lamw = dl[:nseedw].cpu().numpy()
+    for s_ in range(0, nseedw, 8):
+        lo, ito, _ = oracle.pcg(Sw[s_], Pw[s_], gw[s_], np.zeros(wN * wnx, np.float32), wnx, wN, wtol, wmax)
+        assert abs(int(itsw[s_]) - ito) <= 1
+        if int(itsw[s_]) == ito:
+            worst = max(worst, float(np.linalg.norm(lamw[s_].astype(np.float64) - lo) / np.linalg.norm(lo)))
+    assert worst <= 1e-5, worst
+    other["N64_batched"] = {"batch": nbw, "nx": wnx, "knot_points": wN, "dtype": "float32", "iters_mean": float(itsw.mean()), "ms_per_launch": msw,
+                            "solves_per_s": nbw / (msw * 1e-3), "bytes_per_solve": bw, "roofline_frac": bw * nbw / (msw * 1e-3) / 1e9 / peak,
+                            "hbm_line_solves_per_s": peak * 1e9 / bw, "kernel": pw["kernel"], "cluster": pw["cluster"], "threads": pw["threads"],
+                            "parity_max_rel_err_vs_oracle": worst}
+    del dS, dP, dg, dl, di
     out["other_configs"] = other
 
     # ---- device-resident preconditioner build (events) ----

@@ -383,8 +383,10 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
             bool wide_wins = false;
             if (wide) {
                 Plan rp;
-                wide_wins = plan_fused<T>(nx, N, has_p, cfg, batch, &rp) && rp.base_cluster > 1 &&
-                            (unsigned long long)batch * (unsigned long long)rp.base_cluster > (unsigned long long)device_sms();
+                // (against a register-row plan of ONE CTA it is still 10-15 % ahead once every SM has a system: nx 8, N 80: 0.62 -> 0.55 ms)
+                wide_wins = plan_fused<T>(nx, N, has_p, cfg, batch, &rp) &&
+                            (rp.base_cluster > 1 ? (unsigned long long)batch * (unsigned long long)rp.base_cluster > (unsigned long long)device_sms()
+                                                 : (unsigned long long)batch >= (unsigned long long)device_sms());
             }
             if (big4 || wide_wins || (!wide && fills && (tp.rpt == 4 || N * nx / 2 > 64))) {
                 *out = tp;
