@@ -10,3 +10,7 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:pcg_tmem4 -c 1 -f -o gpurun_out/ncu_tmem4_${R} python scripts/prof_kernel.py batched 8192 > gpurun_out/ncu_tmem4_${R}.log 2>&1; tail -2 gpurun_out/ncu_tmem4_${R}.log
 timeout 300 python scripts/time_grid.py 2>&1 | tee gpurun_out/grid_${R}.txt
 timeout 300 python scripts/stress_tmem.py 100 2>&1 | tail -3 | tee gpurun_out/stress_tmem_${R}.txt
+timeout 300 python scripts/time_tmem64.py 2>&1 | grep -v tmem_b | tee gpurun_out/tmem64_${R}.txt | cut -c1-120
+timeout 300 python scripts/time_tmem4_wide.py 2>&1 | tee gpurun_out/tmem4_wide_${R}.txt | cut -c1-120
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:pcg_tmem4 -c 1 -f -o gpurun_out/ncu_tmem4_wide_${R} python scripts/time_tmem4_wide.py 4096 > gpurun_out/ncu_tmem4_wide_${R}.log 2>&1; tail -2 gpurun_out/ncu_tmem4_wide_${R}.log
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:pcg_fused -c 1 -f -o gpurun_out/ncu_tmem64_${R} python scripts/prof_kernel.py batched64 2048 > gpurun_out/ncu_tmem64_${R}.log 2>&1; tail -2 gpurun_out/ncu_tmem64_${R}.log
