@@ -69,6 +69,7 @@ struct Plan {
     const RowsVariant *v = nullptr;
     int cluster = 1, bpc = 0, threads = 0, nbuf = 1, pmode = P_NONE;
     int base_cluster = 1;             // cluster size the planner fitted before latency mode promoted it (pcg_fused)
+    int ctas_per_sm = 1;              // P_TMEM form of pcg_fused: 2 for the CTAs of at most 128 threads (SMs per system = cluster / ctas_per_sm)
     size_t smem = 0;
     const void *fn = nullptr;
     const char *name = "";
@@ -195,29 +196,39 @@ static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_
                          GBDPCG_FLAG_LEGACY_ROWS))
             return false;
         const FusedVariant *tab = nullptr;
-        int cnt = 0, pair = 0, sk = 0;
+        int cnt = 0, pair = 0;
+        int sk4[4] = {0, 0, 0, 0};
         if (const char *e = getenv("GBDPCG_TMEM64_VARIANT")) pair = atoi(e) ? 1 : 0;      // tuning knob (A/B runs)
         switch (nx) {
-#define CASE(NX) case NX: tab = fused_tmem_variants_f64_##NX(&cnt); sk = fused_tmem_sk_f64_##NX(pair); break;
+#define CASE(NX) case NX: tab = fused_tmem_variants_f64_##NX(&cnt); for (int i = 0; i < 4; i++) sk4[i] = fused_tmem_sk_f64_##NX(i); break;
             GBDPCG_FOR_EACH_NX_TMEM64(CASE)
 #undef CASE
             default: break;
         }
-        if (cnt < 2 * pair + 2) return false;
-        const int cpt = 2 * 2 * (3 * (int)nx + sk);                                       // tensor-memory columns per thread
+        if (cnt < 8) return false;
+        // Two shapes of CTA at the smallest cluster that fits: up to 256 threads with the SM to itself, or -- when the CTAs have at most 128
+        // threads anyway -- the 128-thread kernel with a 256-column allocation, so that TWO CTAs of two different systems share an SM and
+        // cover each other's reduction and exchange phases (nx 16, N 32: 1.28 -> 0.84 ms per 2048).  Halving the CTAs on purpose (twice the
+        // cluster) does not pay: C3 2.09 against 1.94 ms.  GBDPCG_TMEM64_SMALL=0 keeps one CTA per SM (A/B runs).
+        const char *es = getenv("GBDPCG_TMEM64_SMALL");
+        const bool allow_small = es ? atoi(es) != 0 : true;
         static const int cl_opts[] = {1, 2, 4, 8, 16};
         for (int cl : cl_opts) {
             if (cfg.cluster && (int)cfg.cluster != cl) continue;
             const int bpc = ((int)N + cl - 1) / cl;
             const int threads = round_up(bpc * ((int)nx / 2), 32);
-            const FusedVariant *v = &tab[2 * pair + (cl > 1 ? 1 : 0)];
-            if (threads > v->maxt || ((threads + 127) / 128) * cpt > 512) continue;
-            const size_t smem = make_fused_plan<T>((int)nx, v->nxp, bpc, P_TMEM, 1).total;
-            if (smem > kMaxDynSmem) continue;
-            out->generic = false; out->fused_kernel = true; out->tmem_kernel = false; out->grid_kernel = false; out->v = nullptr;
-            out->cluster = cl; out->base_cluster = cl; out->bpc = bpc; out->threads = threads; out->nbuf = 1; out->pmode = P_TMEM;
-            out->smem = smem; out->fn = v->fn; out->name = v->name; out->rpt = 2; out->fused = 1;
-            return true;
+            for (int small = (allow_small && threads <= 128) ? 1 : 0; small >= 0; small--) {
+                const int cpt = 2 * 2 * (3 * (int)nx + sk4[pair + 2 * small]);                // tensor-memory columns per thread
+                const FusedVariant *v = &tab[4 * small + 2 * pair + (cl > 1 ? 1 : 0)];
+                if (threads > v->maxt || ((v->maxt + 127) / 128) * cpt > 512) continue;
+                const size_t smem = make_fused_plan<T>((int)nx, v->nxp, bpc, P_TMEM, 1).total;
+                if (smem > kMaxDynSmem) continue;
+                if (small && (2 * (smem + 1024) > 233472 || cpt > 256)) continue;              // two per SM or it is pointless
+                out->generic = false; out->fused_kernel = true; out->tmem_kernel = false; out->grid_kernel = false; out->v = nullptr;
+                out->cluster = cl; out->base_cluster = cl; out->bpc = bpc; out->threads = threads; out->nbuf = 1; out->pmode = P_TMEM;
+                out->smem = smem; out->fn = v->fn; out->name = v->name; out->rpt = 2; out->fused = 1; out->ctas_per_sm = small ? 2 : 1;
+                return true;
+            }
         }
         return false;
     }
@@ -404,7 +415,8 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
             const bool have_reg = plan_fused<T>(nx, N, has_p, cfg, batch, &rp);
             const bool throughput = (unsigned long long)batch * (unsigned long long)(have_reg ? rp.base_cluster : 1) > (unsigned long long)device_sms();
             // (equal cluster sizes: still ahead where the register-row plan has to keep Phi^-1 in shared memory -- nx 16, N 32: 2.14 -> 1.29 ms)
-            if (have_reg && throughput && (tp.cluster < rp.base_cluster || (tp.cluster == rp.base_cluster && rp.pmode == P_SMEM))) {
+            const int tp_sms2 = 2 * tp.cluster / tp.ctas_per_sm, rp_sms2 = 2 * rp.base_cluster;      // SMs per system, doubled
+            if (have_reg && throughput && (tp_sms2 < rp_sms2 || (tp_sms2 == rp_sms2 && rp.pmode == P_SMEM))) {
                 *out = tp;
                 return GBDPCG_OK;
             }
@@ -464,7 +476,7 @@ static std::vector<FnState> g_fn_ready;
 struct OccState { const void *fn; int device, cluster, threads; size_t smem; int resident; };
 static std::vector<OccState> g_occ;
 
-static int prepare_fn(const void *fn, bool clustered)
+static int prepare_fn(const void *fn, bool clustered, bool max_carveout = false)
 {
     int dev;
     CK(cudaGetDevice(&dev));
@@ -473,6 +485,8 @@ static int prepare_fn(const void *fn, bool clustered)
         if (s.fn == fn && s.device == dev) return GBDPCG_OK;
     CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem));
     if (clustered) CK(cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    // half-size CTAs of the tensor-memory form: two of ~80 KB must be able to share an SM (the default carveout for that request holds one)
+    if (max_carveout) CK(cudaFuncSetAttribute(fn, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     g_fn_ready.push_back({fn, dev, clustered});
     return GBDPCG_OK;
 }
@@ -501,7 +515,7 @@ static int max_resident_problems(const Plan &p, int *out)
     } else if (p.cluster == 1) {
         int per_sm = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, p.fn, p.threads, p.smem));
-        *out = per_sm * sms;
+        *out = per_sm * sms * p.ctas_per_sm;
     } else {
         cudaLaunchConfig_t lc = {};
         lc.gridDim = dim3(p.cluster);
@@ -513,7 +527,7 @@ static int max_resident_problems(const Plan &p, int *out)
         lc.attrs = at; lc.numAttrs = 1;
         int ncl = 0;
         CK(cudaOccupancyMaxActiveClusters(&ncl, p.fn, &lc));
-        *out = ncl;
+        *out = ncl * p.ctas_per_sm;
     }
     std::lock_guard<std::mutex> lk(g_fn_mu);
     g_occ.push_back({p.fn, dev, p.cluster, p.threads, p.smem, *out});
@@ -551,7 +565,7 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
                   uint32_t batch, const gbdpcg_config &cfg, uint32_t *d_iters, uint8_t *d_exits, cudaStream_t stream)
 {
     if (batch == 0) return GBDPCG_OK;
-    int rc = prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel);
+    int rc = prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel, p.ctas_per_sm > 1);
     if (rc) return rc;
     int resident = 0;
     rc = max_resident_problems(p, &resident);
@@ -1208,7 +1222,7 @@ static int plan_query(uint32_t nx, uint32_t N, int has_pinv, uint32_t batch, con
     int dev_count = 0;
     if (cudaGetDeviceCount(&dev_count) == cudaSuccess && dev_count > 0) {
         int res = 0;
-        if (prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel) == GBDPCG_OK && max_resident_problems(p, &res) == GBDPCG_OK) out->max_resident = res;
+        if (prepare_fn(p.fn, p.cluster > 1 && !p.grid_kernel, p.ctas_per_sm > 1) == GBDPCG_OK && max_resident_problems(p, &res) == GBDPCG_OK) out->max_resident = res;
     } else {
         cudaGetLastError();
     }

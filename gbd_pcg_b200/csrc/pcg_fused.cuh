@@ -545,12 +545,13 @@ __device__ __forceinline__ double fma_t(double a, double b, double c) { return _
 // the kernel
 // ---------------------------------------------------------------------------------------------
 template <typename T, int NX, int R, int PMODE, bool FUSED, bool CLUSTERED, int MAXT, int SK = 0>
-__global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> a)
+__global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1) pcg_fused_kernel(const KernelArgs<T> a)
 {
     static_assert(NX % R == 0, "rows per thread must divide the state size");
     constexpr bool TM = (PMODE == P_TMEM);                                      // Phi^-1 rows (and SK columns of S) in tensor memory
     static_assert(!TM || (FUSED && sizeof(T) == 8 && MAXT <= 256), "P_TMEM: fp64, single-reduction recurrence, at most two warps per lane quarter");
     static_assert(TM || SK == 0, "SK belongs to P_TMEM");
+    static_assert(!TM || ((MAXT + 127) / 128) * TmGeo<T, NX, R, TM ? SK : 0>::CPT <= 512, "the warps of a lane quarter share its 512 tensor-memory columns");
     using TG = TmGeo<T, NX, R, TM ? SK : 0>;
     constexpr int NXP = Geo<T>::nxp(NX);
     constexpr int BSZ = 3 * NX * NX;
@@ -620,7 +621,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
     (void)tbase_s;
     if constexpr (TM) {
         if (warp == 0) {
-            const uint32_t ncols = (uint32_t)tm_alloc_cols(TG::CPT, (int)blockDim.x);
+            constexpr uint32_t ncols = (uint32_t)tm_alloc_cols(TG::CPT, MAXT);         // from MAXT, not blockDim: 256 columns for the half-size CTAs
             asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tbase_s)), "r"(ncols) : "memory");
             asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
         }
@@ -1121,7 +1122,7 @@ __global__ void __launch_bounds__(MAXT, 1) pcg_fused_kernel(const KernelArgs<T> 
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         if (warp == 0) {
-            const uint32_t ncols = (uint32_t)tm_alloc_cols(TG::CPT, (int)blockDim.x);
+            constexpr uint32_t ncols = (uint32_t)tm_alloc_cols(TG::CPT, MAXT);
             asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tbase), "r"(ncols) : "memory");
         }
     }

@@ -15,7 +15,7 @@ namespace gbdpcg {
 #define STR_(x) #x
 #define STR(x) STR_(x)
 constexpr int NX = INST_NX;
-constexpr int MAXT = 256;      // 8 warps: two per tensor-memory lane quarter
+constexpr int MAXT_BIG = 256;  // 8 warps: two per tensor-memory lane quarter
 // Panel columns of S that go to tensor memory beside Phi^-1: what the register file cannot hold (2 rows x 3nx doubles of S are 12nx
 // registers; vectors, accumulators, window pairs and two tensor-memory chunks need about 130 more: nx 14 with 12 columns -> 250
 // registers, no spills; with 8 -> 255 and 48 bytes of spills; one chunk more measured equal or up to 4 % faster on every state
@@ -27,15 +27,25 @@ constexpr int MAXT = 256;      // 8 warps: two per tensor-memory lane quarter
 #define INST_SK_B ((INST_SK_A) + 4)
 #endif
 constexpr int SK_A = INST_SK_A, SK_B = INST_SK_B;
+// CTAs of at most 128 threads (one warp per lane quarter) allocate 256 columns, so that TWO of them share an SM: Phi^-1 (12 nx columns)
+// plus the S tail must fit those 256
+constexpr int sk_small(int sk) { return (12 * NX + 4 * sk <= 256) ? sk : (256 - 12 * NX) / 16 * 4; }
+constexpr int SKS_A = sk_small(SK_A), SKS_B = sk_small(SK_B);
+constexpr int MAXT_SMALL = 128;
+// (nx 16: two warps of a lane quarter would need 2 x 288 columns -- its "big" kernels are 128-thread ones too, alone on their SM)
+constexpr int MAXT = (2 * (12 * NX + 4 * SK_B) <= 512) ? MAXT_BIG : MAXT_SMALL;
 
-#define VARIANT(CL, SKV, SKNAME)                                                                              \
-    {NX, 1, 2, CL, P_TMEM, 1, MAXT, Geo<double>::nxp(NX),                                                       \
-     (const void *)pcg_fused_kernel<double, NX, 2, P_TMEM, true, (CL != 0), MAXT, SKV>,                       \
+#define VARIANT(CL, MT, SKV, SKNAME)                                                                          \
+    {NX, 1, 2, CL, P_TMEM, 1, MT, Geo<double>::nxp(NX),                                                         \
+     (const void *)pcg_fused_kernel<double, NX, 2, P_TMEM, true, (CL != 0), MT, SKV>,                         \
      "pcg_fused<f64,nx=" STR(INST_NX) ",R=2," #CL ",P_TMEM,S_tmem=" SKNAME ">"}
 
+// [0..3]: up to 256 threads, one CTA per SM; [4..7]: up to 128 threads, two CTAs per SM.  Each: (one CTA, clustered) x (choice a, b).
 static const FusedVariant g_table[] = {
-    VARIANT(0, SK_A, "a"), VARIANT(1, SK_A, "a"),
-    VARIANT(0, SK_B, "b"), VARIANT(1, SK_B, "b"),
+    VARIANT(0, MAXT, SK_A, "a"), VARIANT(1, MAXT, SK_A, "a"),
+    VARIANT(0, MAXT, SK_B, "b"), VARIANT(1, MAXT, SK_B, "b"),
+    VARIANT(0, MAXT_SMALL, SKS_A, "a,2 per SM"), VARIANT(1, MAXT_SMALL, SKS_A, "a,2 per SM"),
+    VARIANT(0, MAXT_SMALL, SKS_B, "b,2 per SM"), VARIANT(1, MAXT_SMALL, SKS_B, "b,2 per SM"),
 };
 
 const FusedVariant *CAT2(fused_tmem_variants_f64_, INST_NX)(int *count)
@@ -43,7 +53,7 @@ const FusedVariant *CAT2(fused_tmem_variants_f64_, INST_NX)(int *count)
     *count = (int)(sizeof g_table / sizeof g_table[0]);
     return g_table;
 }
-// columns of S in tensor memory of entry pair 0 / 1 (the planner sizes the allocation check with it)
-int CAT2(fused_tmem_sk_f64_, INST_NX)(int pair) { return pair == 0 ? SK_A : SK_B; }
+// columns of S in tensor memory: entry pair 0 / 1 of the 256-thread kernels, 2 / 3 of the 128-thread ones
+int CAT2(fused_tmem_sk_f64_, INST_NX)(int pair) { return pair == 0 ? SK_A : pair == 1 ? SK_B : pair == 2 ? SKS_A : SKS_B; }
 
 }  // namespace gbdpcg

@@ -93,7 +93,8 @@ def _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags=0):
     return d_l.cpu().numpy(), d_it.cpu().numpy(), d_ex.cpu().numpy()
 
 
-@pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 64, 300), (14, 7, 64, 75), (14, 7, 32, 500), (12, 4, 100, 200), (8, 4, 200, 333), (14, 7, 100, 97)])
+@pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 64, 300), (14, 7, 64, 75), (14, 7, 32, 500), (12, 4, 100, 200), (8, 4, 200, 333), (14, 7, 100, 97),
+                                           (14, 7, 16, 700), (8, 4, 32, 901), (16, 8, 32, 310), (10, 5, 24, 333)])   # CTAs of <= 128 threads: two per SM
 @pytest.mark.parametrize("precond", ["stair", "jacobi"])
 def test_tmem64_batches_vs_oracle_and_register_kernel(nx, nu, N, batch, precond):
     """The planner's choice for fp64 batches that cannot be resident at once (more clusters than the GPU holds): ragged batch sizes,
@@ -109,6 +110,10 @@ def test_tmem64_batches_vs_oracle_and_register_kernel(nx, nu, N, batch, precond)
     sms = torch.cuda.get_device_properties(0).multi_processor_count
     if batch * info_reg["cluster"] > sms:
         assert "P_TMEM" in info["kernel"] and info["cluster"] <= info_reg["cluster"], (info, info_reg)
+    forced = g.plan_query(nx, N, F64, True, g.pcg_config(empty_pinv=0, flags=g._lib.FLAG_TMEM), batch=batch)
+    assert ("2 per SM" in forced["kernel"]) == (forced["threads"] <= 128), forced
+    if forced["threads"] <= 128:
+        assert forced["max_resident"] * forced["cluster"] > sms                       # more CTAs resident than there are SMs
     lam0 = np.zeros((batch, N * nx))
     lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags=g._lib.FLAG_TMEM)
     lam_r, it_r, ex_r = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags=g._lib.FLAG_NO_TMEM)
