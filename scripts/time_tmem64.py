@@ -14,16 +14,19 @@ import gbd_pcg_b200 as g  # noqa: E402
 FLAG_TMEM, FLAG_NO_TMEM = 0x400, 0x800
 batch = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
 nseed = 32
-SHAPES = [(14, 7, 64), (14, 7, 32), (12, 4, 100), (8, 4, 200), (10, 5, 60), (16, 8, 32)]
+SHAPES = [(14, 7, 64), (14, 7, 32), (12, 4, 100), (8, 4, 200), (10, 5, 60), (16, 8, 32),
+          (14, 7, 16), (8, 4, 32), (12, 4, 20), (16, 8, 16)]      # the last four: CTAs of <= 128 threads, two per SM
 for (nx, nu, N) in SHAPES:
     S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), "stair", np.float64)
     d_S, d_P, d_g = (torch.from_numpy(a).cuda().repeat(batch // nseed, 1) for a in (S, P, gam))
     out = {}
-    for name, flags, env in (("regs", FLAG_NO_TMEM, None), ("tmem_a", FLAG_TMEM, None), ("tmem_b", FLAG_TMEM, "1"), ("planner", 0, None)):
-        if env is not None:
+    for name, flags, env in (("regs", FLAG_NO_TMEM, None), ("tmem_a", FLAG_TMEM, None), ("tmem_b", FLAG_TMEM, "1"), ("tmem_1sm", FLAG_TMEM, "one"), ("planner", 0, None)):
+        os.environ.pop("GBDPCG_TMEM64_VARIANT", None)
+        os.environ.pop("GBDPCG_TMEM64_SMALL", None)
+        if env == "one":
+            os.environ["GBDPCG_TMEM64_SMALL"] = "0"          # one CTA per SM even where the CTAs have <= 128 threads
+        elif env is not None:
             os.environ["GBDPCG_TMEM64_VARIANT"] = env
-        else:
-            os.environ.pop("GBDPCG_TMEM64_VARIANT", None)
         d_l = torch.zeros(batch, N * nx, dtype=torch.float64, device="cuda")
         d_it = torch.zeros(batch, dtype=torch.int32, device="cuda")
         d_ex = torch.zeros(batch, dtype=torch.uint8, device="cuda")
@@ -45,6 +48,7 @@ for (nx, nu, N) in SHAPES:
                 ts.append(a.elapsed_time(b))
         out[name] = (float(np.median(ts)), d_l.cpu().numpy(), d_it.cpu().numpy(), info)
     os.environ.pop("GBDPCG_TMEM64_VARIANT", None)
+    os.environ.pop("GBDPCG_TMEM64_SMALL", None)
     ref = out.get("regs")
     for name, (t, l, it, info) in out.items():
         agree = "" if ref is None else f"  iters equal to regs {bool(np.array_equal(it, ref[2]))}  rel diff {np.linalg.norm(l - ref[1]) / np.linalg.norm(ref[1]):.2e}"
