@@ -1,7 +1,7 @@
 // pcg_fused.cuh -- the sm_100a PCG kernel (second generation of this library's hot path).
 //
 // One thread-block cluster (1..16 CTAs) owns one system for the whole solve and is persistent over a
-// batch of systems.  A thread owns R rows (R = 2 for fp32, 1 for fp64) of the (N*nx)-dimensional system
+// batch of systems.  A thread owns R rows (R = 2 for fp32, 1 for fp64; 2 in the fp64 P_TMEM form) of the (N*nx)-dimensional system
 // and keeps those rows of S and Phi^-1 in REGISTERS; lambda, r, p, ... live in registers too.  The only
 // data that moves per iteration is the vector being multiplied: it is published into a small shared
 // "window" (own block-rows + one halo block on each side; the halo of the neighbouring CTA is written
@@ -22,6 +22,10 @@
 // thread re-sums the same partials in the same order, so alpha, beta and the exit decision are
 // bit-identical in every thread of every CTA (the reference gets this from re-reducing d_eta_new_temp in
 // every block, include/pcg.cuh:189-195).  There is no grid.sync and no global-memory traffic inside the loop.
+//
+// Where Phi^-1 lives (PMODE): P_REG registers (the default where both matrices fit), P_SMEM resident in shared memory, P_NONE identity,
+// P_TMEM tensor memory -- the fp64 throughput form: two rows per thread, the rows of Phi^-1 and the tail of the rows of S in TMEM, half
+// the SMs per system (TmGeo / tm_* below; instantiated in pcg_fused_tmem_inst.cu).
 //
 // Batched mode: while a system is being solved, the NEXT system's S and Phi^-1 block-rows are prefetched
 // into shared memory by the TMA engine (cp.async.bulk + mbarrier), so HBM latency is hidden behind the
