@@ -978,11 +978,13 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
     for (size_t o = 0; o < batch; o += chunk, ci++) {
         const size_t n = (batch - o < chunk) ? batch - o : chunk;
         cudaStream_t st = w->streams[ci & 1];
-        if ((rc = upload_S<T>(dS + o * me, hS + o * me, nx, N, n, cfg, st))) return rc;
-        if (bk >= 0) { if ((rc = build_pinv_dev<T>(dS + o * me, dP + o * me, nx, N, (uint32_t)n, bk, st))) return rc; }
-        else if (has_p) CK(cudaMemcpyAsync(dP + o * me, hP + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
+        // every H2D copy of the chunk before its first kernel: a copy queued behind the chunk's own sym_fill / builder kernels would sit at
+        // the head of the copy engine's queue until they finish and hold back the next chunk's S
         CK(cudaMemcpyAsync(dg + o * ve, hg + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(dl + o * ve, hl + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
+        if (bk < 0 && has_p) CK(cudaMemcpyAsync(dP + o * me, hP + o * me, sizeof(T) * me * n, cudaMemcpyHostToDevice, st));
+        if ((rc = upload_S<T>(dS + o * me, hS + o * me, nx, N, n, cfg, st))) return rc;
+        if (bk >= 0) { if ((rc = build_pinv_dev<T>(dS + o * me, dP + o * me, nx, N, (uint32_t)n, bk, st))) return rc; }
         rc = launch<T>(p, dS + o * me, has_p ? dP + o * me : nullptr, dg + o * ve, dl + o * ve, nx, N, (uint32_t)n, *cfg,
                        w->d_iters + o, w->d_exits + o, st);
         if (rc) return rc;

@@ -26,8 +26,8 @@ for _ in range(5):
 torch.cuda.synchronize()
 dt = (time.perf_counter() - t0) / 5
 print(f"raw pinned H2D of S: {S.nbytes / dt / 1e9:.1f} GB/s ({dt * 1e3:.2f} ms)")
-cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, flags=_lib.FLAG_BUILD_STAIR)
-for parts in (4, 8, 16, 32, 64):
+for sym, parts in [(s_, p_) for s_ in (0, 1) for p_ in (4, 8, 16, 32)]:
+    cfg = g.pcg_config(pcg_exit_tol=1e-6, pcg_max_iter=1000, flags=_lib.FLAG_BUILD_STAIR | (_lib.FLAG_SYMMETRIC_S if sym else 0))
     os.environ["GBDPCG_HOST_CHUNKS"] = str(parts)
     for _ in range(2):
         hl[:] = 0; g.solve_batched_host(hS, None, hg, hl, nx, N, batch, cfg)
@@ -35,4 +35,4 @@ for parts in (4, 8, 16, 32, 64):
     for _ in range(5):
         hl[:] = 0
         t0 = time.perf_counter(); g.solve_batched_host(hS, None, hg, hl, nx, N, batch, cfg); ts.append(time.perf_counter() - t0)
-    print(f"chunks={parts}: {np.median(ts) * 1e3:.2f} ms -> {batch / np.median(ts) / 1e3:.1f} k solves/s")
+    print(f"symmetric shipping {sym} chunks={parts}: {np.median(ts) * 1e3:.2f} ms -> {batch / np.median(ts) / 1e3:.1f} k solves/s")
