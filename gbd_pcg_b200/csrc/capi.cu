@@ -974,10 +974,20 @@ static int solve_batched_host(gbdpcg_workspace *user_ws, const T *hS, const T *h
         gbdpcg_workspace *w; bool armed = true;
         ~Drain() { if (armed) { cudaStreamSynchronize(w->streams[0]); cudaStreamSynchronize(w->streams[1]); cudaGetLastError(); } }
     } drain{w};
+    // The run is H2D-bound: what the caller waits for after the last byte has crossed PCIe is the LAST piece's builder + solve + D2H, so the
+    // last chunk is cut in two (down to one resident wave) -- its first half computes while the second half is still arriving.
+    std::vector<std::pair<size_t, size_t>> pieces;
+    for (size_t o = 0; o < batch; o += chunk) pieces.push_back({o, (batch - o < chunk) ? batch - o : chunk});
+    if (pieces.back().second >= 2 * (size_t)resident) {
+        const std::pair<size_t, size_t> last = pieces.back();
+        const size_t tail = (last.second / 2) / (size_t)resident * (size_t)resident;      // whole waves, at least one (last.second >= 2 waves)
+        pieces.back() = {last.first, last.second - tail};
+        pieces.push_back({last.first + last.second - tail, tail});
+    }
     int ci = 0;
-    for (size_t o = 0; o < batch; o += chunk, ci++) {
-        const size_t n = (batch - o < chunk) ? batch - o : chunk;
-        cudaStream_t st = w->streams[ci & 1];
+    for (const auto &pc : pieces) {
+        const size_t o = pc.first, n = pc.second;
+        cudaStream_t st = w->streams[ci++ & 1];
         // every H2D copy of the chunk before its first kernel: a copy queued behind the chunk's own sym_fill / builder kernels would sit at
         // the head of the copy engine's queue until they finish and hold back the next chunk's S
         CK(cudaMemcpyAsync(dg + o * ve, hg + o * ve, sizeof(T) * ve * n, cudaMemcpyHostToDevice, st));
