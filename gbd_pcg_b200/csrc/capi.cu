@@ -363,6 +363,9 @@ static bool plan_tmem(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
     return true;
 }
 
+static int prepare_fn(const void *fn, bool clustered, bool max_carveout = false);   // below: per-(device, kernel) attributes
+static int max_resident_problems(const Plan &p, int *out);                         // below: occupancy of a plan on the current device
+
 template <typename T>
 static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, uint32_t batch, Plan *out)
 {
@@ -420,6 +423,29 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
                 *out = tp;
                 return GBDPCG_OK;
             }
+            // Latency mode (every system of the batch gets its own cluster in one wave): the tensor-memory form on the LARGEST cluster whose CTAs
+            // keep two warps -- two rows per thread halve the threads a CTA has to synchronise and the window traffic.  Single solves, p50 against
+            // the register-row latency plan: C3 55.4 -> 49.4 us, nx 8 x N 200 57.4 -> 45.1, nx 14 x N 128 59.6 -> 53.2, nx 12 x N 100 51.2 -> 49.3;
+            // nx 10 and 16 measured 2-4 % behind, they keep the register rows.
+            if (!throughput && nx != 10 && nx != 16 && !getenv("GBDPCG_TMEM64_NO_LATENCY")) {
+                for (int cl = 16; cl >= 2; cl >>= 1) {
+                    if ((unsigned long long)batch * (unsigned long long)cl > (unsigned long long)device_sms()) continue;
+                    const int bpc = ((int)N + cl - 1) / cl;
+                    if (round_up(bpc * ((int)nx / 2), 32) < 64 || (cl - 1) * bpc >= (int)N) continue;   // two warps per CTA, no empty CTA
+                    gbdpcg_config c2 = cfg;
+                    c2.cluster = (uint32_t)cl;
+                    Plan lp;
+                    int res = 0;
+                    if (!plan_fused_tmem64<T>(nx, N, has_p, c2, &lp)) continue;
+                    // the whole batch must be resident at once with this cluster, or the register-row plan (which steps down by itself) stays
+                    if (prepare_fn(lp.fn, lp.cluster > 1, lp.ctas_per_sm > 1) != GBDPCG_OK || max_resident_problems(lp, &res) != GBDPCG_OK || (uint32_t)res < batch) {
+                        cudaGetLastError();
+                        break;
+                    }
+                    *out = lp;
+                    return GBDPCG_OK;
+                }
+            }
         }
     }
     if (!(cfg.flags & (GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS)) && plan_fused<T>(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK;
@@ -476,7 +502,7 @@ static std::vector<FnState> g_fn_ready;
 struct OccState { const void *fn; int device, cluster, threads; size_t smem; int resident; };
 static std::vector<OccState> g_occ;
 
-static int prepare_fn(const void *fn, bool clustered, bool max_carveout = false)
+static int prepare_fn(const void *fn, bool clustered, bool max_carveout)
 {
     int dev;
     CK(cudaGetDevice(&dev));
