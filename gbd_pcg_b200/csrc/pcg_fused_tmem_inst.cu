@@ -19,7 +19,7 @@ constexpr int MAXT_BIG = 256;  // 8 warps: two per tensor-memory lane quarter
 // Panel columns of S that go to tensor memory beside Phi^-1: what the register file cannot hold (2 rows x 3nx doubles of S are 12nx
 // registers; vectors, accumulators, window pairs and two tensor-memory chunks need about 130 more: nx 14 with 12 columns -> 250
 // registers, no spills; with 8 -> 255 and 48 bytes of spills; one chunk more measured equal or up to 4 % faster on every state
-// size, profiles/tmem64_r2n.txt).  A/B alternative in the second pair.
+// size, profiles/tmem64_r2r.txt).  A/B alternative in the second pair.
 #ifndef INST_SK_A
 #define INST_SK_A (((12 * INST_NX > 120) ? ((12 * INST_NX - 120 + 15) / 16 * 4) : 0) + 4)
 #endif
