@@ -185,12 +185,13 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
 // columns of the rows of S in tensor memory -- a system needs half the SMs of the register-row plan (C3: a 2-CTA cluster of 224
 // threads instead of 4 CTAs).  The smallest cluster whose CTAs fit 256 threads, the shared-memory limit (staging holds one matrix
 // at a time) and 512 tensor-memory columns.
+// (fp32, state sizes that are multiples of 4: the same form with FOUR rows per thread -- same words of S per thread, same columns)
 template <typename T>
 static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
 {
-    if constexpr (sizeof(T) != 8) {
-        return false;
-    } else {
+    constexpr bool f64 = sizeof(T) == 8;
+    constexpr int RPT = f64 ? 2 : 4;
+    {
         if (!has_p) return false;
         if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_PINV_SMEM | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_NO_TMA | GBDPCG_FLAG_FORCE_GENERIC |
                          GBDPCG_FLAG_LEGACY_ROWS))
@@ -199,11 +200,20 @@ static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_
         int cnt = 0, pair = 0;
         int sk4[4] = {0, 0, 0, 0};
         if (const char *e = getenv("GBDPCG_TMEM64_VARIANT")) pair = atoi(e) ? 1 : 0;      // tuning knob (A/B runs)
-        switch (nx) {
+        if constexpr (f64) {
+            switch (nx) {
 #define CASE(NX) case NX: tab = fused_tmem_variants_f64_##NX(&cnt); for (int i = 0; i < 4; i++) sk4[i] = fused_tmem_sk_f64_##NX(i); break;
-            GBDPCG_FOR_EACH_NX_TMEM64(CASE)
+                GBDPCG_FOR_EACH_NX_TMEM64(CASE)
 #undef CASE
-            default: break;
+                default: break;
+            }
+        } else {
+            switch (nx) {
+#define CASE(NX) case NX: tab = fused_tmem_variants_f32_##NX(&cnt); for (int i = 0; i < 4; i++) sk4[i] = fused_tmem_sk_f32_##NX(i); break;
+                GBDPCG_FOR_EACH_NX_TMEM32(CASE)
+#undef CASE
+                default: break;
+            }
         }
         if (cnt < 8) return false;
         // Two shapes of CTA at the smallest cluster that fits: up to 256 threads with the SM to itself, or -- when the CTAs have at most 128
@@ -216,7 +226,7 @@ static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_
         for (int cl : cl_opts) {
             if (cfg.cluster && (int)cfg.cluster != cl) continue;
             const int bpc = ((int)N + cl - 1) / cl;
-            const int threads = round_up(bpc * ((int)nx / 2), 32);
+            const int threads = round_up(bpc * ((int)nx / RPT), 32);
             for (int small = (allow_small && threads <= 128) ? 1 : 0; small >= 0; small--) {
                 const int cpt = 2 * 2 * (3 * (int)nx + sk4[pair + 2 * small]);                // tensor-memory columns per thread
                 const FusedVariant *v = &tab[4 * small + 2 * pair + (cl > 1 ? 1 : 0)];
@@ -226,7 +236,7 @@ static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_
                 if (small && (2 * (smem + 1024) > 233472 || cpt > 256)) continue;              // two per SM or it is pointless
                 out->generic = false; out->fused_kernel = true; out->tmem_kernel = false; out->grid_kernel = false; out->v = nullptr;
                 out->cluster = cl; out->base_cluster = cl; out->bpc = bpc; out->threads = threads; out->nbuf = 1; out->pmode = P_TMEM;
-                out->smem = smem; out->fn = v->fn; out->name = v->name; out->rpt = 2; out->fused = 1; out->ctas_per_sm = small ? 2 : 1;
+                out->smem = smem; out->fn = v->fn; out->name = v->name; out->rpt = RPT; out->fused = 1; out->ctas_per_sm = small ? 2 : 1;
                 return true;
             }
         }
@@ -374,8 +384,8 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     int cnt;
     all_variants(f64, (int)nx, &tab, &cnt);
     if (cfg.flags & GBDPCG_FLAG_TMEM) {
-        if constexpr (!f64) { if (plan_tmem(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK; }
-        else { if (plan_fused_tmem64<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK; }
+        if constexpr (!f64) { if (!cfg.cluster && plan_tmem(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK; }
+        if (plan_fused_tmem64<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK;
         return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: Phi^-1 given and fp32, even nx <= 16, N*ceil(nx/4) <= 256 threads -- or fp64, even nx 8..16, "
                     "N*nx/2 <= 16 x 256 threads (nx=%u N=%u %s)", nx, N, f64 ? "f64" : "f32");
     }
@@ -408,9 +418,11 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
             }
         }
     }
-    // fp64 throughput mode: a batch whose register-row clusters cannot all be resident at once takes the tensor-memory form of the
-    // fused kernel when that needs fewer SMs per system (C3 x 2048: 2-CTA clusters instead of 4-CTA ones)
-    if constexpr (f64) {
+    // Throughput mode of everything the kernels above do not take (fp64; fp32 systems beyond 256 four-row threads, nx a multiple of 4): a
+    // batch whose register-row clusters cannot all be resident at once takes the tensor-memory form of the fused kernel when that needs
+    // fewer SMs per system (C3 x 2048: 2-CTA clusters instead of 4-CTA ones, 3.61 -> 1.94 ms; fp32 C4 x 2048: 8 CTAs instead of 16,
+    // 9.62 -> 5.78 ms; nx 8 x N 200 fp32: 2.23 -> 1.01 ms)
+    {
         const uint32_t auto_off = GBDPCG_FLAG_NO_TMEM | GBDPCG_FLAG_FORCE_GENERIC | GBDPCG_FLAG_LEGACY_ROWS | GBDPCG_FLAG_PINV_REG | GBDPCG_FLAG_PINV_SMEM |
                                   GBDPCG_FLAG_TEXTBOOK | GBDPCG_FLAG_NO_TMA;
         Plan tp, rp;
@@ -426,12 +438,14 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
             // Latency mode (every system of the batch gets its own cluster in one wave): the tensor-memory form on the LARGEST cluster whose CTAs
             // keep two warps -- two rows per thread halve the threads a CTA has to synchronise and the window traffic.  Single solves, p50 against
             // the register-row latency plan: C3 55.4 -> 49.4 us, nx 8 x N 200 57.4 -> 45.1, nx 14 x N 128 59.6 -> 53.2, nx 12 x N 100 51.2 -> 49.3;
-            // nx 10 and 16 measured 2-4 % behind, they keep the register rows.
-            if (!throughput && nx != 10 && nx != 16 && !getenv("GBDPCG_TMEM64_NO_LATENCY")) {
+            // nx 10 and 16 measured 2-4 % behind, they keep the register rows.  fp32 (four rows per thread): nx 8 and 16 gain 13-16 % (nx 8 x N 200
+            // 38.9 -> 32.9 us, nx 8 x N 512 41.0 -> 34.8, nx 16 x N 100 45.1 -> 39.0, nx 16 x N 64 45.2 -> 38.9), nx 12 loses (N 100: 30.7 -> 34.8; C4 equal).
+            const bool latency_ok = f64 ? (nx != 10 && nx != 16) : (nx == 8 || nx == 16);
+            if (!throughput && latency_ok && !getenv("GBDPCG_TMEM64_NO_LATENCY")) {
                 for (int cl = 16; cl >= 2; cl >>= 1) {
                     if ((unsigned long long)batch * (unsigned long long)cl > (unsigned long long)device_sms()) continue;
                     const int bpc = ((int)N + cl - 1) / cl;
-                    if (round_up(bpc * ((int)nx / 2), 32) < 64 || (cl - 1) * bpc >= (int)N) continue;   // two warps per CTA, no empty CTA
+                    if (round_up(bpc * ((int)nx / (f64 ? 2 : 4)), 32) < 64 || (cl - 1) * bpc >= (int)N) continue;   // two warps per CTA, no empty CTA
                     gbdpcg_config c2 = cfg;
                     c2.cluster = (uint32_t)cl;
                     Plan lp;

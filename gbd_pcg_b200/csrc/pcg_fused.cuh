@@ -422,15 +422,21 @@ __host__ __device__ constexpr int tm_alloc_cols(int cpt, int threads)
     const int need = ((threads + 127) / 128) * cpt;     // warps per lane quarter x columns per thread
     return need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 512;
 }
-__device__ __forceinline__ uint32_t tm_lo(double x) { return (uint32_t)__double2loint(x); }
-__device__ __forceinline__ uint32_t tm_hi(double x) { return (uint32_t)__double2hiint(x); }
+__device__ __forceinline__ float fma_t(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double fma_t(double a, double b, double c) { return __fma_rn(a, b, c); }
+// element <-> 32-bit tensor-memory words (one for float, two for double), and element e of a 16-byte window vector
+__device__ __forceinline__ void tm_pack(uint32_t *v, float x) { v[0] = __float_as_uint(x); }
+__device__ __forceinline__ void tm_pack(uint32_t *v, double x) { v[0] = (uint32_t)__double2loint(x); v[1] = (uint32_t)__double2hiint(x); }
+__device__ __forceinline__ void tm_unpack(const uint32_t *v, float &x) { x = __uint_as_float(v[0]); }
+__device__ __forceinline__ void tm_unpack(const uint32_t *v, double &x) { x = __hiloint2double((int)v[1], (int)v[0]); }
+__device__ __forceinline__ float tm_vec_get(const float4 &v, int e) { return e == 0 ? v.x : e == 1 ? v.y : e == 2 ? v.z : v.w; }
+__device__ __forceinline__ double tm_vec_get(const double2 &v, int e) { return e == 0 ? v.x : v.y; }
 
 // rows M[row][k], k in [KB, KE)  ->  tensor-memory columns from taddr on
 template <typename T, int NX, int R, int KB, int KE>
 __device__ __forceinline__ void tm_store_rows(const T (&M)[R][3 * NX], uint32_t taddr)
 {
-    static_assert(sizeof(T) == 8, "P_TMEM is the fp64 mode");
-    constexpr int CPK = R * 2, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC;
+    constexpr int W32 = (int)sizeof(T) / 4, CPK = R * W32, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC;
     static_assert(REM == 0 || REM * CPK == 8, "the last chunk is whole or a half");
 #pragma unroll
     for (int c = 0; c < NFULL; c++) {
@@ -438,10 +444,7 @@ __device__ __forceinline__ void tm_store_rows(const T (&M)[R][3 * NX], uint32_t 
 #pragma unroll
         for (int kk = 0; kk < KPC; kk++)
 #pragma unroll
-            for (int row = 0; row < R; row++) {
-                v[(kk * R + row) * 2] = tm_lo(M[row][KB + c * KPC + kk]);
-                v[(kk * R + row) * 2 + 1] = tm_hi(M[row][KB + c * KPC + kk]);
-            }
+            for (int row = 0; row < R; row++) tm_pack(&v[(kk * R + row) * W32], M[row][KB + c * KPC + kk]);
         tmem_st16(taddr + 16 * c, v);
     }
     if constexpr (REM != 0) {
@@ -449,10 +452,7 @@ __device__ __forceinline__ void tm_store_rows(const T (&M)[R][3 * NX], uint32_t 
 #pragma unroll
         for (int kk = 0; kk < REM; kk++)
 #pragma unroll
-            for (int row = 0; row < R; row++) {
-                v[(kk * R + row) * 2] = tm_lo(M[row][KB + NFULL * KPC + kk]);
-                v[(kk * R + row) * 2 + 1] = tm_hi(M[row][KB + NFULL * KPC + kk]);
-            }
+            for (int row = 0; row < R; row++) tm_pack(&v[(kk * R + row) * W32], M[row][KB + NFULL * KPC + kk]);
         tmem_st8(taddr + 16 * NFULL, v);
     }
 }
@@ -462,21 +462,23 @@ __device__ __forceinline__ void tm_store_rows(const T (&M)[R][3 * NX], uint32_t 
 template <typename T, int NX, int R, int NCH, int KB, int KE>
 __device__ __forceinline__ void tm_mv_part(uint32_t taddr, const T *__restrict__ w, T (&acc)[R][NCH])
 {
-    static_assert(sizeof(T) == 8 && NX % 2 == 0 && KB % 2 == 0, "fp64, window pairs never straddle a block");
+    constexpr int V = Geo<T>::V;                          // elements per 16-byte window load (4 floats, 2 doubles)
+    static_assert(NX % V == 0 && KB % V == 0, "window vectors never straddle a block");
+    using Vec = typename Vec16<T>::type;
     constexpr int NXP = Geo<T>::nxp(NX);
-    constexpr int CPK = R * 2, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC, NCHUNK = NFULL + (REM ? 1 : 0);
-    static_assert(KPC % 2 == 0 && REM % 2 == 0, "whole window pairs per chunk");
+    constexpr int W32 = (int)sizeof(T) / 4, CPK = R * W32, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC, NCHUNK = NFULL + (REM ? 1 : 0);
+    static_assert(KPC % V == 0 && REM % V == 0, "whole window vectors per chunk");
     if constexpr (NCHUNK > 0) {
         uint32_t u[2][16];
-        double2 x[2][KPC / 2];
-        auto issue = [&](int c, uint32_t (&dst)[16], double2 (&xd)[KPC / 2]) {
+        Vec x[2][KPC / V];
+        auto issue = [&](int c, uint32_t (&dst)[16], Vec (&xd)[KPC / V]) {
             const int nk = (c < NFULL) ? KPC : REM;
             if (nk == KPC) tmem_ld16(taddr + 16 * c, dst);
             else tmem_ld8(taddr + 16 * c, dst);
 #pragma unroll
-            for (int h = 0; h < KPC / 2; h++) {
-                const int k = KB + c * KPC + 2 * h;
-                if (2 * h < nk) xd[h] = *reinterpret_cast<const double2 *>(w + (k / NX) * NXP + (k % NX));
+            for (int h = 0; h < KPC / V; h++) {
+                const int k = KB + c * KPC + V * h;
+                if (V * h < nk) xd[h] = *reinterpret_cast<const Vec *>(w + (k / NX) * NXP + (k % NX));
             }
         };
         issue(0, u[0], x[0]);
@@ -490,11 +492,12 @@ __device__ __forceinline__ void tm_mv_part(uint32_t taddr, const T *__restrict__
             for (int kk = 0; kk < KPC; kk++) {
                 if (kk < nk) {
                     const int k = KB + c * KPC + kk;
-                    const double xv = (kk & 1) ? x[c & 1][kk / 2].y : x[c & 1][kk / 2].x;
+                    const T xv = tm_vec_get(x[c & 1][kk / V], kk % V);
 #pragma unroll
                     for (int row = 0; row < R; row++) {
-                        const double m = __hiloint2double((int)u[c & 1][(kk * R + row) * 2 + 1], (int)u[c & 1][(kk * R + row) * 2]);
-                        acc[row][k % NCH] = __fma_rn(m, xv, acc[row][k % NCH]);
+                        T m;
+                        tm_unpack(&u[c & 1][(kk * R + row) * W32], m);
+                        acc[row][k % NCH] = fma_t(m, xv, acc[row][k % NCH]);
                     }
                 }
             }
@@ -506,25 +509,27 @@ __device__ __forceinline__ void tm_mv_part(uint32_t taddr, const T *__restrict__
 template <typename T, int NX, int R, int NCH, int KE>
 __device__ __forceinline__ void tm_reg_part(const T (&M)[R][3 * NX], const T *__restrict__ w, T (&acc)[R][NCH])
 {
-    static_assert(sizeof(T) == 8 && NX % 2 == 0 && KE % 2 == 0, "fp64, window pairs never straddle a block");
+    constexpr int V = Geo<T>::V;
+    static_assert(NX % V == 0 && KE % V == 0, "window vectors never straddle a block");
+    using Vec = typename Vec16<T>::type;
     constexpr int NXP = Geo<T>::nxp(NX);
-    constexpr int GRP = 8;                                  // panel columns whose window pairs are loaded together
+    constexpr int GRP = 8;                                  // panel columns whose window vectors are loaded together
 #pragma unroll
     for (int g = 0; g < KE; g += GRP) {
-        double2 x[GRP / 2];
+        Vec x[GRP / V];
 #pragma unroll
-        for (int h = 0; h < GRP / 2; h++) {
-            const int k = g + 2 * h;
-            if (k < KE) x[h] = *reinterpret_cast<const double2 *>(w + (k / NX) * NXP + (k % NX));
+        for (int h = 0; h < GRP / V; h++) {
+            const int k = g + V * h;
+            if (k < KE) x[h] = *reinterpret_cast<const Vec *>(w + (k / NX) * NXP + (k % NX));
         }
         asm volatile("" ::: "memory");
 #pragma unroll
         for (int kk = 0; kk < GRP; kk++) {
             const int k = g + kk;
             if (k < KE) {
-                const double xv = (kk & 1) ? x[kk / 2].y : x[kk / 2].x;
+                const T xv = tm_vec_get(x[kk / V], kk % V);
 #pragma unroll
-                for (int row = 0; row < R; row++) acc[row][k % NCH] = __fma_rn(M[row][k], xv, acc[row][k % NCH]);
+                for (int row = 0; row < R; row++) acc[row][k % NCH] = fma_t(M[row][k], xv, acc[row][k % NCH]);
             }
         }
     }
@@ -542,8 +547,6 @@ __device__ long long g_trace_fix[16][8];
 #define XTRACE(m) do { } while (0)
 #endif
 
-__device__ __forceinline__ float fma_t(float a, float b, float c) { return __fmaf_rn(a, b, c); }
-__device__ __forceinline__ double fma_t(double a, double b, double c) { return __fma_rn(a, b, c); }
 
 // ---------------------------------------------------------------------------------------------
 // the kernel
@@ -553,7 +556,8 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
 {
     static_assert(NX % R == 0, "rows per thread must divide the state size");
     constexpr bool TM = (PMODE == P_TMEM);                                      // Phi^-1 rows (and SK columns of S) in tensor memory
-    static_assert(!TM || (FUSED && sizeof(T) == 8 && MAXT <= 256), "P_TMEM: fp64, single-reduction recurrence, at most two warps per lane quarter");
+    static_assert(!TM || (FUSED && MAXT <= 256 && (sizeof(T) == 8 ? R == 2 : (R == 4 && NX % 4 == 0))),
+                  "P_TMEM: single-reduction recurrence, at most two warps per lane quarter; fp64 with two rows per thread, fp32 with four (nx a multiple of 4)");
     static_assert(TM || SK == 0, "SK belongs to P_TMEM");
     static_assert(!TM || ((MAXT + 127) / 128) * TmGeo<T, NX, R, TM ? SK : 0>::CPT <= 512, "the warps of a lane quarter share its 512 tensor-memory columns");
     using TG = TmGeo<T, NX, R, TM ? SK : 0>;
@@ -655,7 +659,8 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
     const bool send_next = CLUSTERED && active && lb == nb - 1 && rank < last_rank;
 
     auto put = [&](T *dst, const T (&x)[R]) {
-        if constexpr (R == 2 && sizeof(T) == 4) *reinterpret_cast<float2 *>(dst) = make_float2(x[0], x[1]);
+        if constexpr (R == 4 && sizeof(T) == 4) *reinterpret_cast<float4 *>(dst) = make_float4(x[0], x[1], x[2], x[3]);
+        else if constexpr (R == 2 && sizeof(T) == 4) *reinterpret_cast<float2 *>(dst) = make_float2(x[0], x[1]);
         else if constexpr (R == 2 && sizeof(T) == 8) *reinterpret_cast<double2 *>(dst) = make_double2(x[0], x[1]);
         else {
 #pragma unroll
@@ -777,6 +782,9 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
                 } else if constexpr (R == 2 && sizeof(T) == 8) {
                     const double2 q = *reinterpret_cast<const double2 *>(row + k * NX);
                     M[0][k] = q.x; M[1][k] = q.y;
+                } else if constexpr (R == 4 && sizeof(T) == 4 && NX % 4 == 0) {
+                    const float4 q = *reinterpret_cast<const float4 *>(row + k * NX);
+                    M[0][k] = q.x; M[1][k] = q.y; M[2][k] = q.z; M[3][k] = q.w;
                 } else {
 #pragma unroll
                     for (int i = 0; i < R; i++) M[i][k] = row[k * NX + i];

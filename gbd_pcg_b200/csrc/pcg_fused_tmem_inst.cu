@@ -1,6 +1,7 @@
-// pcg_fused_tmem_inst.cu -- instantiates the fp64 throughput form of the fused kernel (pcg_fused.cuh, PMODE = P_TMEM): two rows
-// per thread, Phi^-1 rows and the last SK panel columns of the S rows in tensor memory.  Compiled once per state size with
-// -DINST_NX=<nx> (see csrc/Makefile).
+// pcg_fused_tmem_inst.cu -- instantiates the tensor-memory form of the fused kernel (pcg_fused.cuh, PMODE = P_TMEM): Phi^-1 rows and the
+// last SK panel columns of the S rows in tensor memory; fp64 with two rows per thread, fp32 (-DINST_F32=1, nx a multiple of 4) with four --
+// either way 12 nx words of S and 4 (3 nx + SK) tensor-memory columns per thread.  Compiled once per (dtype, state size) with
+// -DINST_NX=<nx> [-DINST_F32=1] (see csrc/Makefile).
 #include "kernel_table.h"
 #include "pcg_fused.cuh"
 
@@ -10,6 +11,24 @@
 
 namespace gbdpcg {
 
+#ifndef INST_F32
+#define INST_F32 0
+#endif
+#if INST_F32
+typedef float InstT;
+constexpr int RPT = 4;
+#define INST_DT "f32"
+#define INST_RS "4"
+#define TABLE_NAME CAT2(fused_tmem_variants_f32_, INST_NX)
+#define SK_NAME CAT2(fused_tmem_sk_f32_, INST_NX)
+#else
+typedef double InstT;
+constexpr int RPT = 2;
+#define INST_DT "f64"
+#define INST_RS "2"
+#define TABLE_NAME CAT2(fused_tmem_variants_f64_, INST_NX)
+#define SK_NAME CAT2(fused_tmem_sk_f64_, INST_NX)
+#endif
 #define CAT2_(a, b) a##b
 #define CAT2(a, b) CAT2_(a, b)
 #define STR_(x) #x
@@ -36,9 +55,9 @@ constexpr int MAXT_SMALL = 128;
 constexpr int MAXT = (2 * (12 * NX + 4 * SK_B) <= 512) ? MAXT_BIG : MAXT_SMALL;
 
 #define VARIANT(CL, MT, SKV, SKNAME)                                                                          \
-    {NX, 1, 2, CL, P_TMEM, 1, MT, Geo<double>::nxp(NX),                                                         \
-     (const void *)pcg_fused_kernel<double, NX, 2, P_TMEM, true, (CL != 0), MT, SKV>,                         \
-     "pcg_fused<f64,nx=" STR(INST_NX) ",R=2," #CL ",P_TMEM,S_tmem=" SKNAME ">"}
+    {NX, !INST_F32, RPT, CL, P_TMEM, 1, MT, Geo<InstT>::nxp(NX),                                                \
+     (const void *)pcg_fused_kernel<InstT, NX, RPT, P_TMEM, true, (CL != 0), MT, SKV>,                        \
+     "pcg_fused<" INST_DT ",nx=" STR(INST_NX) ",R=" INST_RS "," #CL ",P_TMEM,S_tmem=" SKNAME ">"}
 
 // [0..3]: up to 256 threads, one CTA per SM; [4..7]: up to 128 threads, two CTAs per SM.  Each: (one CTA, clustered) x (choice a, b).
 static const FusedVariant g_table[] = {
@@ -48,12 +67,12 @@ static const FusedVariant g_table[] = {
     VARIANT(0, MAXT_SMALL, SKS_B, "b,2 per SM"), VARIANT(1, MAXT_SMALL, SKS_B, "b,2 per SM"),
 };
 
-const FusedVariant *CAT2(fused_tmem_variants_f64_, INST_NX)(int *count)
+const FusedVariant *TABLE_NAME(int *count)
 {
     *count = (int)(sizeof g_table / sizeof g_table[0]);
     return g_table;
 }
 // columns of S in tensor memory: entry pair 0 / 1 of the 256-thread kernels, 2 / 3 of the 128-thread ones
-int CAT2(fused_tmem_sk_f64_, INST_NX)(int pair) { return pair == 0 ? SK_A : pair == 1 ? SK_B : pair == 2 ? SKS_A : SKS_B; }
+int SK_NAME(int pair) { return pair == 0 ? SK_A : pair == 1 ? SK_B : pair == 2 ? SKS_A : SKS_B; }
 
 }  // namespace gbdpcg

@@ -225,3 +225,70 @@ def test_tmem64_variant_b_and_concurrent_launches():
         g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, l2, cfg, stream=s2)
         torch.cuda.synchronize()
         assert np.array_equal(l1.cpu().numpy(), lam_a) and np.array_equal(l2.cpu().numpy(), lam_a)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# the same form in fp32: FOUR rows per thread (state sizes that are multiples of 4), for systems beyond the single-CTA
+# tensor-memory kernels (more than 256 four-row threads) -- C4-sized systems on 8 CTAs instead of 16
+# ---------------------------------------------------------------------------------------------------------------
+F32 = np.float32
+
+
+def _check32(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex):
+    lam_o, it_o, ex_o = oracle.pcg(S, P, gam, lam0, nx, N, tol, max_iter, order=0)
+    assert abs(int(it) - it_o) <= 1, (it, it_o)
+    lam_eq = lam_o if it == it_o else oracle_at_iters(S, P, gam, lam0, nx, N, int(it))
+    assert rel_err(lam, lam_eq) <= LAMBDA_TOL[np.dtype(F32)], (rel_err(lam, lam_eq), it, it_o)
+
+
+@pytest.mark.parametrize("nx,nu,N,cluster", [(12, 4, 512, 16), (12, 4, 512, 8), (8, 4, 200, 4), (8, 4, 200, 16), (16, 8, 100, 8), (16, 8, 100, 4),
+                                             (12, 6, 70, 2), (8, 4, 33, 1), (16, 8, 7, 2), (12, 4, 2, 1)])
+@pytest.mark.parametrize("precond", ["stair", "jacobi"])
+def test_tmem32_cluster_form_single_solves(nx, nu, N, cluster, precond):
+    S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, F32, 1e-6, 3000), precond, seed=9)
+    kw = dict(flags=g._lib.FLAG_TMEM, cluster=cluster)
+    info = g.plan_query(nx, N, F32, True, g.pcg_config(empty_pinv=0, **kw))
+    assert "P_TMEM" in info["kernel"] and "R=4" in info["kernel"] and info["cluster"] == cluster, info
+    lam0 = np.zeros(N * nx, F32)
+    lam, it, ex = _solve1(S, P, gam, lam0, nx, N, tol, max_iter, **kw)
+    assert not ex
+    if N * nx > 64:
+        _check32(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex)
+    lam2, it2, _ = _solve1(S, P, gam, lam0, nx, N, tol, max_iter, **kw)
+    assert it2 == it and np.array_equal(lam2, lam)
+
+
+@pytest.mark.parametrize("nx,nu,N,batch", [(12, 4, 100, 301), (8, 4, 200, 222), (16, 8, 100, 160), (12, 4, 300, 60)])
+@pytest.mark.parametrize("precond", ["stair", "jacobi"])
+def test_tmem32_cluster_form_batches(nx, nu, N, batch, precond):
+    torch = _torch()
+    nseed, tol, max_iter = 4, 1e-6, 3000
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(nseed), precond, F32)
+    idx = np.arange(batch) % nseed
+    d_S, d_P, d_g = (torch.from_numpy(a[idx].copy()).cuda() for a in (S, P, gam))
+    auto = g.plan_query(nx, N, F32, True, g.pcg_config(empty_pinv=0), batch=batch)
+    reg = g.plan_query(nx, N, F32, True, g.pcg_config(empty_pinv=0, flags=g._lib.FLAG_NO_TMEM), batch=batch)
+    # the planner's choice in throughput mode: fewer SMs per system (a smaller cluster, or the same with two CTAs per SM)
+    assert "P_TMEM" in auto["kernel"] and (auto["cluster"] < reg["cluster"] or "2 per SM" in auto["kernel"]), (auto, reg)
+    lam0 = np.zeros((batch, N * nx), F32)
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter)
+    lam_r, it_r, ex_r = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, max_iter, flags=g._lib.FLAG_NO_TMEM)
+    assert not ex.any() and not ex_r.any()
+    for s_ in range(nseed):
+        rows = np.nonzero(idx == s_)[0]
+        assert (it[rows] == it[rows[0]]).all() and all(np.array_equal(lam[r], lam[rows[0]]) for r in rows)
+        _check32(S[s_], P[s_], gam[s_], lam0[0], nx, N, tol, max_iter, lam[rows[0]], it[rows[0]], ex[rows[0]])
+        assert abs(int(it[rows[0]]) - int(it_r[rows[0]])) <= 1
+
+
+def test_tmem32_selection():
+    q = lambda nx, N, batch, **kw: g.plan_query(nx, N, F32, True, g.pcg_config(empty_pinv=0, **kw), batch=batch)
+    # latency mode: nx 8 and 16 take the tensor-memory form, nx 12 keeps the register rows (measured); single-CTA shapes keep their kernels
+    assert "P_TMEM" in q(8, 200, 1)["kernel"] and "P_TMEM" in q(16, 100, 1)["kernel"] and "P_TMEM" in q(16, 64, 1)["kernel"]
+    assert "P_TMEM" not in q(12, 512, 1)["kernel"] and "P_TMEM" not in q(12, 100, 1)["kernel"]
+    assert "pcg_tmem4" in q(16, 32, 1)["kernel"] and "pcg_tmem4" in q(12, 40, 8192)["kernel"] and "wide" in q(16, 64, 4096)["kernel"]
+    assert "P_TMEM" in q(12, 512, 2048)["kernel"] and q(12, 512, 2048)["cluster"] == 8
+    assert "P_TMEM" not in q(12, 512, 2048, flags=g._lib.FLAG_NO_TMEM)["kernel"]
+    assert "P_TMEM" not in q(14, 100, 2048)["kernel"]                    # nx not a multiple of 4: no four-row cluster form
+    with pytest.raises(g.GbdpcgError):
+        q(14, 100, 2048, flags=g._lib.FLAG_TMEM)
