@@ -587,6 +587,42 @@ def single_gpu_extras(torch, g, _lib, S, P, gam, cfg, cfg_build, d_S, d_P, d_it,
                             "hbm_line_solves_per_s": peak * 1e9 / bw, "kernel": pw["kernel"], "cluster": pw["cluster"], "threads": pw["threads"],
                             "parity_max_rel_err_vs_oracle": worst}
     del dS, dP, dg, dl, di
+
+    # ---- fp32 batch of C4-sized systems: 1024 x (nx 12, N 512, fp32, tol 1e-6, stair) -- beyond the single-CTA tensor-memory kernels: the
+    #      four-row tensor-memory form of the cluster kernel, 8 CTAs per system where the register-row plan needs 16 ----
+    cnx, cnu, cN, cdt, ctol, cmax = g.synth.CONFIGS["C4"]
+    nbc, nseedc = 1024, 16
+    Sc, Pc, gc = g.synth.lqr_schur_batch(cnx, cnu, cN, range(nseedc), "stair", np.float32)
+    dS, dP, dg = (torch.from_numpy(a).cuda().repeat(nbc // nseedc, 1) for a in (Sc, Pc, gc))
+    dl = torch.zeros(nbc, cN * cnx, dtype=torch.float32, device="cuda")
+    di = torch.zeros(nbc, dtype=torch.int32, device="cuda")
+    ccfg = g.pcg_config(pcg_exit_tol=ctol, pcg_max_iter=cmax, empty_pinv=0)
+
+    def stepc():
+        g.solve_batched_dev(cnx, cN, nbc, dS, dP, dg, dl, ccfg, di, None)
+    for _ in range(3):
+        dl.zero_()
+        stepc()
+    sync()
+    ev = timed_launches(torch, stepc, dl.zero_, 10)
+    sync()
+    msc = st.mean(a.elapsed_time(b) for a, b in ev)
+    bc = layout.algorithmic_bytes(cnx, cN, 4, True)
+    pc = g.plan_query(cnx, cN, np.float32, True, ccfg, batch=nbc)
+    worst = 0.0
+    itsc = di.cpu().numpy()
+    lamc = dl[:nseedc].cpu().numpy()
+    for s_ in range(0, nseedc, 4):
+        lo, ito, _ = oracle.pcg(Sc[s_], Pc[s_], gc[s_], np.zeros(cN * cnx, np.float32), cnx, cN, ctol, cmax)
+        assert abs(int(itsc[s_]) - ito) <= 1
+        if int(itsc[s_]) == ito:
+            worst = max(worst, float(np.linalg.norm(lamc[s_].astype(np.float64) - lo) / np.linalg.norm(lo)))
+    assert worst <= 1e-5, worst
+    other["C4_batched"] = {"batch": nbc, "nx": cnx, "knot_points": cN, "dtype": "float32", "iters_mean": float(itsc.mean()), "ms_per_launch": msc,
+                           "solves_per_s": nbc / (msc * 1e-3), "bytes_per_solve": bc, "roofline_frac": bc * nbc / (msc * 1e-3) / 1e9 / peak,
+                           "hbm_line_solves_per_s": peak * 1e9 / bc, "kernel": pc["kernel"], "cluster": pc["cluster"], "threads": pc["threads"],
+                           "parity_max_rel_err_vs_oracle": worst}
+    del dS, dP, dg, dl, di
     out["other_configs"] = other
 
     # ---- device-resident preconditioner build (events) ----
