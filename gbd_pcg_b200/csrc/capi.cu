@@ -185,7 +185,8 @@ static bool plan_fused(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config 
 // columns of the rows of S in tensor memory -- a system needs half the SMs of the register-row plan (C3: a 2-CTA cluster of 224
 // threads instead of 4 CTAs).  The smallest cluster whose CTAs fit 256 threads, the shared-memory limit (staging holds one matrix
 // at a time) and 512 tensor-memory columns.
-// (fp32, state sizes that are multiples of 4: the same form with FOUR rows per thread -- same words of S per thread, same columns)
+// (fp32, even state sizes 8..16: the same form with FOUR rows per thread -- same words of S per thread, same columns; nx 10 and 14: the
+// last thread of a block-row owns two padding rows)
 template <typename T>
 static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
 {
@@ -226,7 +227,7 @@ static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_
         for (int cl : cl_opts) {
             if (cfg.cluster && (int)cfg.cluster != cl) continue;
             const int bpc = ((int)N + cl - 1) / cl;
-            const int threads = round_up(bpc * ((int)nx / RPT), 32);
+            const int threads = round_up(bpc * (((int)nx + RPT - 1) / RPT), 32);
             for (int small = (allow_small && threads <= 128) ? 1 : 0; small >= 0; small--) {
                 const int cpt = 2 * 2 * (3 * (int)nx + sk4[pair + 2 * small]);                // tensor-memory columns per thread
                 const FusedVariant *v = &tab[4 * small + 2 * pair + (cl > 1 ? 1 : 0)];
@@ -385,7 +386,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
     all_variants(f64, (int)nx, &tab, &cnt);
     if (cfg.flags & GBDPCG_FLAG_TMEM) {
         if constexpr (!f64) { if (!cfg.cluster && plan_tmem(nx, N, has_p, cfg, batch, out)) return GBDPCG_OK; }
-        if (plan_fused_tmem64<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK;
+        if (!(cfg.flags & GBDPCG_FLAG_TMEM_R2) && plan_fused_tmem64<T>(nx, N, has_p, cfg, out)) return GBDPCG_OK;   // (TMEM_R2 asks for the two-row kernel and nothing else)
         return fail(GBDPCG_ERR_UNSUPPORTED, "GBDPCG_FLAG_TMEM: Phi^-1 given and fp32, even nx <= 16, N*ceil(nx/4) <= 256 threads -- or fp64, even nx 8..16, "
                     "N*nx/2 <= 16 x 256 threads (nx=%u N=%u %s)", nx, N, f64 ? "f64" : "f32");
     }
@@ -431,7 +432,9 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
             const bool throughput = (unsigned long long)batch * (unsigned long long)(have_reg ? rp.base_cluster : 1) > (unsigned long long)device_sms();
             // (equal cluster sizes: still ahead where the register-row plan has to keep Phi^-1 in shared memory -- nx 16, N 32: 2.14 -> 1.29 ms)
             const int tp_sms2 = 2 * tp.cluster / tp.ctas_per_sm, rp_sms2 = 2 * rp.base_cluster;      // SMs per system, doubled
-            if (have_reg && throughput && (tp_sms2 < rp_sms2 || (tp_sms2 == rp_sms2 && rp.pmode == P_SMEM))) {
+            // (fp32: only where the register rows need a cluster -- small fp32 systems already run several per SM on the register-row kernel)
+            const bool in_domain = f64 || rp.base_cluster > 1;
+            if (have_reg && throughput && in_domain && (tp_sms2 < rp_sms2 || (tp_sms2 == rp_sms2 && rp.pmode == P_SMEM))) {
                 *out = tp;
                 return GBDPCG_OK;
             }
@@ -445,7 +448,7 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
                 for (int cl = 16; cl >= 2; cl >>= 1) {
                     if ((unsigned long long)batch * (unsigned long long)cl > (unsigned long long)device_sms()) continue;
                     const int bpc = ((int)N + cl - 1) / cl;
-                    if (round_up(bpc * ((int)nx / (f64 ? 2 : 4)), 32) < 64 || (cl - 1) * bpc >= (int)N) continue;   // two warps per CTA, no empty CTA
+                    if (round_up(bpc * (((int)nx + (f64 ? 1 : 3)) / (f64 ? 2 : 4)), 32) < 64 || (cl - 1) * bpc >= (int)N) continue;   // two warps per CTA, no empty CTA
                     gbdpcg_config c2 = cfg;
                     c2.cluster = (uint32_t)cl;
                     Plan lp;

@@ -67,8 +67,8 @@ GBDPCG_FOR_EACH_NX_EXTRA(GBDPCG_DECLARE_FUSED_EXTRA)
     int fused_tmem_sk_f64_##NX(int pair);
 GBDPCG_FOR_EACH_NX_TMEM64(GBDPCG_DECLARE_FTMEM)
 #undef GBDPCG_DECLARE_FTMEM
-// the same form in fp32, four rows per thread (state sizes that are multiples of 4).  Keep in sync with NX_TMEM32 in the Makefile.
-#define GBDPCG_FOR_EACH_NX_TMEM32(X) X(8) X(12) X(16)
+// the same form in fp32, four rows per thread (nx 10, 14: two padding rows in the last thread of a block-row).  Keep in sync with NX_TMEM32 in the Makefile.
+#define GBDPCG_FOR_EACH_NX_TMEM32(X) X(8) X(10) X(12) X(14) X(16)
 #define GBDPCG_DECLARE_FTMEM32(NX)                                 \
     const FusedVariant *fused_tmem_variants_f32_##NX(int *count);  \
     int fused_tmem_sk_f32_##NX(int pair);

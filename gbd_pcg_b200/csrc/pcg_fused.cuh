@@ -430,6 +430,12 @@ __device__ __forceinline__ void tm_pack(uint32_t *v, double x) { v[0] = (uint32_
 __device__ __forceinline__ void tm_unpack(const uint32_t *v, float &x) { x = __uint_as_float(v[0]); }
 __device__ __forceinline__ void tm_unpack(const uint32_t *v, double &x) { x = __hiloint2double((int)v[1], (int)v[0]); }
 __device__ __forceinline__ float tm_vec_get(const float4 &v, int e) { return e == 0 ? v.x : e == 1 ? v.y : e == 2 ? v.z : v.w; }
+__device__ __forceinline__ float tm_vec_get(const float2 &v, int e) { return e == 0 ? v.x : v.y; }
+// window loads of the P_TMEM mat-vec: 16 bytes where a block is a whole number of them, else 8 (fp32 with nx = 2 mod 4: nx 10, 14)
+template <typename T, int NX> struct TmWin { static constexpr int V = Geo<T>::V; using Vec = typename Vec16<T>::type; };
+template <> struct TmWin<float, 10> { static constexpr int V = 2; using Vec = float2; };
+template <> struct TmWin<float, 14> { static constexpr int V = 2; using Vec = float2; };
+template <> struct TmWin<float, 6> { static constexpr int V = 2; using Vec = float2; };
 __device__ __forceinline__ double tm_vec_get(const double2 &v, int e) { return e == 0 ? v.x : v.y; }
 
 // rows M[row][k], k in [KB, KE)  ->  tensor-memory columns from taddr on
@@ -462,9 +468,9 @@ __device__ __forceinline__ void tm_store_rows(const T (&M)[R][3 * NX], uint32_t 
 template <typename T, int NX, int R, int NCH, int KB, int KE>
 __device__ __forceinline__ void tm_mv_part(uint32_t taddr, const T *__restrict__ w, T (&acc)[R][NCH])
 {
-    constexpr int V = Geo<T>::V;                          // elements per 16-byte window load (4 floats, 2 doubles)
+    constexpr int V = TmWin<T, NX>::V;                    // elements per window load (4 floats or 2 doubles; 2 floats for nx = 2 mod 4)
     static_assert(NX % V == 0 && KB % V == 0, "window vectors never straddle a block");
-    using Vec = typename Vec16<T>::type;
+    using Vec = typename TmWin<T, NX>::Vec;
     constexpr int NXP = Geo<T>::nxp(NX);
     constexpr int W32 = (int)sizeof(T) / 4, CPK = R * W32, KPC = 16 / CPK, NK = KE - KB, NFULL = NK / KPC, REM = NK % KPC, NCHUNK = NFULL + (REM ? 1 : 0);
     static_assert(KPC % V == 0 && REM % V == 0, "whole window vectors per chunk");
@@ -509,9 +515,9 @@ __device__ __forceinline__ void tm_mv_part(uint32_t taddr, const T *__restrict__
 template <typename T, int NX, int R, int NCH, int KE>
 __device__ __forceinline__ void tm_reg_part(const T (&M)[R][3 * NX], const T *__restrict__ w, T (&acc)[R][NCH])
 {
-    constexpr int V = Geo<T>::V;
+    constexpr int V = TmWin<T, NX>::V;
     static_assert(NX % V == 0 && KE % V == 0, "window vectors never straddle a block");
-    using Vec = typename Vec16<T>::type;
+    using Vec = typename TmWin<T, NX>::Vec;
     constexpr int NXP = Geo<T>::nxp(NX);
     constexpr int GRP = 8;                                  // panel columns whose window vectors are loaded together
 #pragma unroll
@@ -554,16 +560,21 @@ __device__ long long g_trace_fix[16][8];
 template <typename T, int NX, int R, int PMODE, bool FUSED, bool CLUSTERED, int MAXT, int SK = 0>
 __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1) pcg_fused_kernel(const KernelArgs<T> a)
 {
-    static_assert(NX % R == 0, "rows per thread must divide the state size");
     constexpr bool TM = (PMODE == P_TMEM);                                      // Phi^-1 rows (and SK columns of S) in tensor memory
-    static_assert(!TM || (FUSED && MAXT <= 256 && (sizeof(T) == 8 ? R == 2 : (R == 4 && NX % 4 == 0))),
-                  "P_TMEM: single-reduction recurrence, at most two warps per lane quarter; fp64 with two rows per thread, fp32 with four (nx a multiple of 4)");
+    static_assert(!TM || (FUSED && MAXT <= 256 && (sizeof(T) == 8 ? R == 2 : (R == 4 && NX % 2 == 0))),
+                  "P_TMEM: single-reduction recurrence, at most two warps per lane quarter; fp64 with two rows per thread, fp32 with four (even nx)");
+    // Rows per thread need not divide the state size in the P_TMEM form: the last thread of a block-row then owns padding rows (nx 14, R 4:
+    // rows 12, 13 and two that do not exist) -- zero matrix rows, zero vector entries, never loaded from or stored to global memory, never
+    // pushed to a neighbour.  The window slot of a block is wide enough for them (NXP >= R * TPB).
+    static_assert(NX % R == 0 || TM, "rows per thread must divide the state size");
+    static_assert(Geo<T>::nxp(NX) >= R * ((NX + R - 1) / R), "the padding rows of the last thread must fit the window slot");
     static_assert(TM || SK == 0, "SK belongs to P_TMEM");
     static_assert(!TM || ((MAXT + 127) / 128) * TmGeo<T, NX, R, TM ? SK : 0>::CPT <= 512, "the warps of a lane quarter share its 512 tensor-memory columns");
     using TG = TmGeo<T, NX, R, TM ? SK : 0>;
     constexpr int NXP = Geo<T>::nxp(NX);
     constexpr int BSZ = 3 * NX * NX;
-    constexpr int TPB = NX / R;                                                 // threads per block-row
+    constexpr int TPB = (NX + R - 1) / R;                                       // threads per block-row
+    constexpr bool PADR = (NX % R) != 0;                                        // the last thread of a block-row has padding rows
     constexpr int NWP = round_up(round_up(MAXT, 32) / 32, 2);                   // warp-partial pairs summed per reduction
     namespace cg = cooperative_groups;
 
@@ -765,7 +776,8 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
         for (int i = 0; i < R; i++) { lam[i] = (T)0; gam[i] = (T)0; }
         if (active) {
 #pragma unroll
-            for (int i = 0; i < R; i++) { lam[i] = a.lambda[vofs + i]; gam[i] = __ldg(a.gamma + vofs + i); }
+            for (int i = 0; i < R; i++)
+                if (!PADR || r0 + i < NX) { lam[i] = a.lambda[vofs + i]; gam[i] = __ldg(a.gamma + vofs + i); }
         }
 
         // ---- matrices: HBM -> shared (TMA, or cooperative loads) -> registers ----
@@ -797,7 +809,7 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
             for (int k = 0; k < 3 * NX; k++) {
                 const bool kill = (k < NX) ? kill_left : (k >= 2 * NX) ? kill_right : kill_mid;
 #pragma unroll
-                for (int i = 0; i < R; i++) M[i][k] = kill ? (T)0 : M[i][k];
+                for (int i = 0; i < R; i++) M[i][k] = (kill || (PADR && r0 + i >= NX)) ? (T)0 : M[i][k];   // (padding rows: whatever was read is dropped)
             }
         };
 
@@ -949,7 +961,8 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
                 if constexpr (R == 2) st_async2(ra, x[0], x[1], rm);
                 else {
 #pragma unroll
-                    for (int i = 0; i < R; i++) st_async(ra + (uint32_t)(i * sizeof(T)), x[i], rm);
+                    for (int i = 0; i < R; i++)
+                        if (!PADR || r0 + i < NX) st_async(ra + (uint32_t)(i * sizeof(T)), x[i], rm);   // (the receiver counts nx elements per side)
                 }
             };
             for (;;) {
@@ -1120,7 +1133,8 @@ __global__ void __launch_bounds__(MAXT, (PMODE == P_TMEM && MAXT <= 128) ? 2 : 1
         // ---- outputs                                                            (pcg.cuh:212-215) ----
         if (active) {
 #pragma unroll
-            for (int i = 0; i < R; i++) a.lambda[vofs + i] = lam[i];
+            for (int i = 0; i < R; i++)
+                if (!PADR || r0 + i < NX) a.lambda[vofs + i] = lam[i];
         }
         if (rank == 0 && t == 0) {
             if (a.iters) a.iters[prob] = it;

@@ -76,7 +76,7 @@ typedef struct gbdpcg_config {
                                            GBDPCG_ERR_UNSUPPORTED for shapes neither covers.  fp64 (even nx 8..16): the tensor-memory form of the cluster
                                            kernel (pcg_fused.cuh, P_TMEM: two rows per thread, Phi^-1 rows in tensor memory, half the SMs per system) --
                                            what the planner itself takes for fp64 batches too large to be resident at once; the same form with four rows
-                                           per thread for fp32 systems of nx 8 / 12 / 16 beyond 256 four-row threads (C4-sized).  Assumes no other
+                                           per thread for fp32 systems of even nx 8..16 beyond 256 four-row threads (nx 14: N > 64; C4-sized).  Assumes no other
                                            tensor-memory user (e.g. a concurrent tcgen05 GEMM on another stream) shares the SMs: tcgen05.alloc blocks
                                            until columns are free */
 #define GBDPCG_FLAG_TMEM_R2 0x1000u     /* with GBDPCG_FLAG_TMEM or the planner's own choice: the two-rows-per-thread tensor-memory kernel (pcg_tmem.cuh) even where the

@@ -53,7 +53,10 @@ for case in range(ncase):
             rows = np.nonzero(idx == s_)[0]
             ok = ok and bool((it[rows] == it[rows[0]]).all()) and all(np.array_equal(lam[r], lam[rows[0]]) for r in rows)
             lo, ito, _ = oracle.pcg(S[s_], P[s_], gam[s_], np.zeros(N * nx, dt), nx, N, tol, 3000)
-            ok = ok and abs(int(it[rows[0]]) - ito) <= 1
+            # (fp32 systems of a few dozen unknowns: the iteration at which |r.Phi^-1 r| crosses the tolerance is order-sensitive -- SURVEY App. E,
+            #  tests judge C1 on the solution for the same reason; +-2 there, +-1 everywhere else)
+            ok = ok and abs(int(it[rows[0]]) - ito) <= (2 if (N * nx <= 200 and dt == np.float32) else 1)
+            if abs(int(it[rows[0]]) - ito) > 1: line += f" [oracle iters {ito}]"
             if int(it[rows[0]]) != ito:
                 lo = oracle.pcg(S[s_], P[s_], gam[s_], np.zeros(N * nx, dt), nx, N, 0.0, int(it[rows[0]]))[0]
             e = float(np.linalg.norm(lam[rows[0]].astype(np.float64) - lo) / np.linalg.norm(lo))
@@ -70,7 +73,7 @@ for case in range(ncase):
             ok = ok and e <= lim
             worst = max(worst, e)
         fail = fail or not ok
-        line += f" | {arm}: {short} err {worst:.1e} {'ok' if ok else 'FAIL'}"
+        line += f" | {arm}: {short} err {worst:.1e} iters {[int(it[np.nonzero(idx == s_)[0][0]]) for s_ in range(nseed)]} ex {int(ex.sum())} {'ok' if ok else 'FAIL'}"
     bad += fail
     print(line, flush=True)
 print("kernels exercised:", seen)

@@ -875,7 +875,7 @@ def test_tmem_kernel_selection_and_refusals():
     # (fp64 + GBDPCG_FLAG_TMEM is the tensor-memory form of the cluster kernel: tests/test_tmem64_gpu.py)
     assert "P_TMEM" in g.plan_query(14, 32, np.float64, True, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=8192)["kernel"]
     for (nx, N, dt, has_p) in [(14, 32, np.float64, False), (14, 32, np.float32, False), (15, 20, np.float32, True), (18, 20, np.float32, True),
-                               (14, 65, np.float32, True)]:        # (beyond 256 four-row threads; 129..256 is the wide form, tests/test_tmem4_wide_gpu.py)
+                               (14, 1100, np.float32, True)]:      # (beyond 16 CTAs x 256 four-row threads; up to there: wide form / cluster form, tests/test_tmem4_wide_gpu.py, test_tmem64_gpu.py)
         with pytest.raises(g.GbdpcgError):
             g.plan_query(nx, N, dt, has_p, g.pcg_config(flags=g._lib.FLAG_TMEM), batch=8192)
     # unaligned S / Pinv: the planner's choice falls back to the register-row kernel, same results

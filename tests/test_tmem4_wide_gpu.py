@@ -94,8 +94,8 @@ def test_wide_tmem4_edge_semantics_and_concurrency():
         g.solve_batched_dev(nx, N, batch, d_S, d_P, d_g, l2, cfg, stream=s2)
         torch.cuda.synchronize()
         assert np.array_equal(l1.cpu().numpy(), lam) and np.array_equal(l2.cpu().numpy(), lam)
-    # refusals: beyond 256 four-row threads, and the two-row arm has no wide form
-    for kw, N_ in ((dict(flags=F), 65), (dict(flags=F | g._lib.FLAG_TMEM_R2), 64)):
-        with pytest.raises(g.GbdpcgError) as e:
-            g.plan_query(nx, N_, F32, True, g.pcg_config(empty_pinv=0, **kw), batch=batch)
-        assert e.value.status == g._lib.ERR_UNSUPPORTED
+    # beyond 256 four-row threads the tensor-memory form of the CLUSTER kernel takes over (tests/test_tmem64_gpu.py); the two-row arm has no wide form
+    assert "P_TMEM" in g.plan_query(nx, 65, F32, True, g.pcg_config(empty_pinv=0, flags=F), batch=batch)["kernel"]
+    with pytest.raises(g.GbdpcgError) as e:
+        g.plan_query(nx, 64, F32, True, g.pcg_config(empty_pinv=0, flags=F | g._lib.FLAG_TMEM_R2), batch=batch)
+    assert e.value.status == g._lib.ERR_UNSUPPORTED

@@ -242,7 +242,10 @@ def _check32(S, P, gam, lam0, nx, N, tol, max_iter, lam, it, ex):
 
 
 @pytest.mark.parametrize("nx,nu,N,cluster", [(12, 4, 512, 16), (12, 4, 512, 8), (8, 4, 200, 4), (8, 4, 200, 16), (16, 8, 100, 8), (16, 8, 100, 4),
-                                             (12, 6, 70, 2), (8, 4, 33, 1), (16, 8, 7, 2), (12, 4, 2, 1)])
+                                             (12, 6, 70, 2), (8, 4, 33, 1), (16, 8, 7, 2), (12, 4, 2, 1),
+                                             # nx = 2 mod 4: the last thread of a block-row owns two padding rows
+                                             (14, 7, 100, 4), (14, 7, 100, 2), (14, 7, 512, 8), (14, 7, 60, 1), (14, 7, 3, 1), (14, 7, 2, 1), (14, 7, 130, 16),
+                                             (10, 5, 150, 4), (10, 5, 33, 2), (10, 5, 85, 1)])
 @pytest.mark.parametrize("precond", ["stair", "jacobi"])
 def test_tmem32_cluster_form_single_solves(nx, nu, N, cluster, precond):
     S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, F32, 1e-6, 3000), precond, seed=9)
@@ -258,7 +261,7 @@ def test_tmem32_cluster_form_single_solves(nx, nu, N, cluster, precond):
     assert it2 == it and np.array_equal(lam2, lam)
 
 
-@pytest.mark.parametrize("nx,nu,N,batch", [(12, 4, 100, 301), (8, 4, 200, 222), (16, 8, 100, 160), (12, 4, 300, 60)])
+@pytest.mark.parametrize("nx,nu,N,batch", [(12, 4, 100, 301), (8, 4, 200, 222), (16, 8, 100, 160), (12, 4, 300, 60), (14, 7, 100, 300), (14, 7, 128, 150)])
 @pytest.mark.parametrize("precond", ["stair", "jacobi"])
 def test_tmem32_cluster_form_batches(nx, nu, N, batch, precond):
     torch = _torch()
@@ -289,6 +292,36 @@ def test_tmem32_selection():
     assert "pcg_tmem4" in q(16, 32, 1)["kernel"] and "pcg_tmem4" in q(12, 40, 8192)["kernel"] and "wide" in q(16, 64, 4096)["kernel"]
     assert "P_TMEM" in q(12, 512, 2048)["kernel"] and q(12, 512, 2048)["cluster"] == 8
     assert "P_TMEM" not in q(12, 512, 2048, flags=g._lib.FLAG_NO_TMEM)["kernel"]
-    assert "P_TMEM" not in q(14, 100, 2048)["kernel"]                    # nx not a multiple of 4: no four-row cluster form
+    assert "P_TMEM" in q(14, 100, 2048)["kernel"] and q(14, 100, 2048)["cluster"] == 2      # nx 14: padded row groups, 2 CTAs instead of 4
+    assert "P_TMEM" not in q(10, 100, 2048)["kernel"]                    # nx 10: no fewer SMs than the register rows -- not taken
+    assert "P_TMEM" not in q(6, 300, 2048)["kernel"]                     # no instantiation below nx 8
     with pytest.raises(g.GbdpcgError):
-        q(14, 100, 2048, flags=g._lib.FLAG_TMEM)
+        q(6, 300, 2048, flags=g._lib.FLAG_TMEM)
+
+
+def test_tmem32_padded_rows_edge_semantics():
+    """nx 14, four rows per thread, N beyond the single-CTA kernels: max_iter 0 / cap / warm start, NaN-poisoned padding blocks, NaN in gamma."""
+    torch = _torch()
+    nx, nu, N, batch, tol = 14, 7, 100, 160, 1e-6
+    S, P, gam = g.synth.lqr_schur_batch(nx, nu, N, range(4), "stair", F32)
+    Sn, Pn = S.copy(), P.copy()
+    for M in (Sn, Pn):
+        M[:, : nx * nx] = np.nan
+        M[:, (N - 1) * 3 * nx * nx + 2 * nx * nx:] = np.nan
+    idx = np.arange(batch) % 4
+    d_S, d_P, d_g = (torch.from_numpy(a[idx].copy()).cuda() for a in (Sn, Pn, gam))
+    lam0 = np.random.default_rng(5).standard_normal((batch, N * nx)).astype(F32)
+    F = g._lib.FLAG_TMEM
+    assert "P_TMEM" in g.plan_query(nx, N, F32, True, g.pcg_config(empty_pinv=0, flags=F), batch=batch)["kernel"]
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, 0, F)
+    assert np.array_equal(lam, lam0) and (it == 0).all() and (ex == 1).all()
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, 3, F)
+    assert (it == 3).all() and (ex == 1).all() and np.isfinite(lam).all()
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, d_g, lam0, tol, 3000, F)
+    assert (ex == 0).all()
+    for i in (0, 1, 2, 3, batch - 1):
+        _check32(S[idx[i]], P[idx[i]], gam[idx[i]], lam0[i], nx, N, tol, 3000, lam[i], it[i], ex[i])
+    gam_n = gam[idx].copy()
+    gam_n[7, 13] = np.nan
+    lam, it, ex = _batched(nx, N, batch, d_S, d_P, torch.from_numpy(gam_n).cuda(), np.zeros((batch, N * nx), F32), tol, 40, F)
+    assert it[7] == 40 and ex[7] == 1 and (ex[np.arange(batch) != 7] == 0).all()
