@@ -429,6 +429,12 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         Plan tp, rp;
         if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_fused_tmem64<T>(nx, N, has_p, cfg, &tp)) {
             const bool have_reg = plan_fused<T>(nx, N, has_p, cfg, batch, &rp);
+            // Beyond what a 16-CTA cluster of register rows holds, a 16-CTA cluster of this form still does (nx 14 fp32: N <= 1024 instead of 832,
+            // fp64 N <= 576 instead of 464): it goes before the cooperative grid -- nx 14 x N 800 fp32 single solve 148.8 -> 58.5 us.
+            if (!have_reg) {
+                *out = tp;
+                return GBDPCG_OK;
+            }
             const bool throughput = (unsigned long long)batch * (unsigned long long)(have_reg ? rp.base_cluster : 1) > (unsigned long long)device_sms();
             // (equal cluster sizes: still ahead where the register-row plan has to keep Phi^-1 in shared memory -- nx 16, N 32: 2.14 -> 1.29 ms)
             const int tp_sms2 = 2 * tp.cluster / tp.ctas_per_sm, rp_sms2 = 2 * rp.base_cluster;      // SMs per system, doubled

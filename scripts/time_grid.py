@@ -45,3 +45,21 @@ for (nx, nu, N, dt, tol) in [(14, 7, 1500, np.float32, 1e-6), (14, 7, 1000, np.f
             itr = int(rk.d_iters.item())
             line += f" | reference pcg<> {tr:8.1f} us, {itr} iterations, {tr / itr:6.2f} us/iteration -> x{tr / t:.2f}"
         print(line, flush=True)
+
+# Between the register-row cluster's limit and the tensor-memory cluster's: the planner's choice (16-CTA cluster, Phi^-1 in tensor
+# memory) next to what GBDPCG_FLAG_NO_TMEM leaves (the cooperative grid).
+print("--- tensor-memory cluster form before the grid ---", flush=True)
+for (nx, nu, N, dt, tol) in [(14, 7, 800, np.float32, 1e-6), (14, 7, 900, np.float32, 1e-6), (14, 7, 1024, np.float32, 1e-6), (12, 4, 1200, np.float32, 1e-6),
+                             (14, 7, 400, np.float64, 1e-10), (14, 7, 576, np.float64, 1e-10), (12, 4, 672, np.float64, 1e-10), (8, 4, 1024, np.float64, 1e-10)]:
+    S, P, gam = g.synth.lqr_schur(nx, nu, N, 1, "stair", dt)
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (S, P, gam))
+    d_l = torch.zeros(N * nx, dtype=d_S.dtype, device="cuda")
+    d_it = torch.zeros(1, dtype=torch.int32, device="cuda")
+    line = f"nx={nx} N={N} {np.dtype(dt).name}:"
+    for flags in (0, g._lib.FLAG_NO_TMEM):
+        cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=5000, empty_pinv=0, flags=flags)
+        info = g.plan_query(nx, N, dt, True, cfg)
+        t = p50(lambda: g.solve_dev_async(nx, N, d_S, d_P, d_g, d_l, cfg, d_it, None), d_l.zero_)
+        it = int(d_it.item())
+        line += f" {info['kernel']} G={info['cluster']} x {info['threads']}: {t:7.1f} us / {it} it = {t / it:5.2f} us/it |"
+    print(line, flush=True)

@@ -73,7 +73,7 @@ def test_plan_query_without_gpu(nx, N, dtype, cluster, spec):
     assert 0 < info["smem_bytes"] <= 227 * 1024
 
 
-@pytest.mark.parametrize("nx,N,dtype", [(14, 1500, np.float32), (14, 1000, np.float64), (12, 1200, np.float32), (14, 833, np.float32), (14, 5328, np.float32)])
+@pytest.mark.parametrize("nx,N,dtype", [(14, 1500, np.float32), (14, 1000, np.float64), (12, 1400, np.float32), (14, 1025, np.float32), (14, 5328, np.float32)])
 def test_plan_query_beyond_one_cluster(nx, N, dtype):
     """Systems no 16-CTA cluster holds go to the cooperative-grid kernel, at most one CTA per SM (the reference accepts any N whose
     N CTAs are co-resident, include/pcg.cuh:23-49: 1776 knot points for nx=14 fp32 on a B200)."""
@@ -81,6 +81,16 @@ def test_plan_query_beyond_one_cluster(nx, N, dtype):
     assert "pcg_grid" in info["kernel"] and info["specialised"] == 1
     assert info["cluster"] <= 148 and info["cluster"] * info["block_rows"] >= N
     assert info["threads"] % 32 == 0 and 64 <= info["threads"] <= 1024 and 0 < info["smem_bytes"] <= 227 * 1024
+
+
+@pytest.mark.parametrize("nx,N,dtype", [(14, 833, np.float32), (14, 1024, np.float32), (12, 1200, np.float32), (14, 576, np.float64), (8, 1024, np.float64)])
+def test_plan_query_tensor_memory_cluster_before_the_grid(nx, N, dtype):
+    """Past the register-row cluster (nx 14 fp32: N <= 752) a 16-CTA cluster with Phi^-1 in tensor memory still holds the system
+    (N <= 1024; fp64 N <= 576): the planner takes it before the cooperative grid; GBDPCG_FLAG_NO_TMEM restores the grid."""
+    info = g.plan_query(nx, N, dtype, True)
+    assert "P_TMEM" in info["kernel"] and info["cluster"] == 16 and info["cluster"] * info["block_rows"] >= N
+    assert info["threads"] % 32 == 0 and info["threads"] <= 256
+    assert "pcg_grid" in g.plan_query(nx, N, dtype, True, g.pcg_config(empty_pinv=0, flags=_lib.FLAG_NO_TMEM))["kernel"]
 
 
 def test_plan_query_rejects_what_cannot_fit():

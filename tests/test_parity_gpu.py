@@ -185,7 +185,7 @@ def test_maximum_knot_points(nx, nu, dt):
     judged by its residual (the dense cross-checks of check_against_oracle do not scale to it) and against the oracle's iteration
     count; one knot point more is refused with GBDPCG_ERR_UNSUPPORTED, never mis-solved."""
     N = _largest_plannable_N(nx, dt)
-    assert N >= 1024                                   # beyond what one 16-CTA cluster holds (832 for nx=14 fp32)
+    assert N >= 1024                                   # beyond what one 16-CTA cluster holds (1024 for nx=14 fp32, Phi^-1 in tensor memory)
     tol = 1e-6 if dt == np.float32 else 1e-10
     S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 4000), "stair", seed=5)
     lam0 = np.zeros(N * nx, dtype=dt)
@@ -209,13 +209,16 @@ GRID_CASES = [(14, 7, 1500, np.float32), (14, 7, 1000, np.float64), (12, 4, 1200
 @pytest.mark.parametrize("nx,nu,N,dt", GRID_CASES)
 @pytest.mark.parametrize("precond", PRECONDS)
 def test_systems_beyond_one_cluster(nx, nu, N, dt, precond):
-    """Systems no 16-CTA cluster can hold (the reference solves them on its cooperative grid, include/pcg.cuh:23-49): the planner
-    takes the cooperative-grid kernel (pcg_grid.cuh); iterations within +-1 of the oracle, lambda at the bar at equal count."""
+    """Systems no 16-CTA cluster of register rows can hold (the reference solves them on its cooperative grid, include/pcg.cuh:23-49):
+    the planner takes the cooperative-grid kernel (pcg_grid.cuh), or first the tensor-memory cluster form where that reaches; iterations within +-1 of the oracle, lambda at the bar at equal count."""
     tol = 1e-6 if dt == np.float32 else 1e-10
     S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 5000), precond, seed=3)
     info = g.plan_query(nx, N, dt, P is not None, g.pcg_config(empty_pinv=0 if P is not None else 1))
     assert info["cluster"] * info["block_rows"] >= N
-    if P is not None or N * nx > 20000:           # (without Phi^-1 a 16-CTA cluster reaches further: S alone in registers)
+    if P is not None and (nx, N) in ((14, 833), (12, 1200)):
+        # past the register-row cluster (nx 14 fp32: N <= 752) a 16-CTA cluster with Phi^-1 in tensor memory still holds the system
+        assert "P_TMEM" in info["kernel"] and info["cluster"] == 16
+    elif P is not None or N * nx > 20000:         # (without Phi^-1 a 16-CTA cluster reaches further: S alone in registers)
         assert "pcg_grid" in info["kernel"] and info["max_resident"] == 1
     lam0 = np.zeros(N * nx, dtype=dt)
     lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
