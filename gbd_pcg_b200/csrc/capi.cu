@@ -1156,7 +1156,26 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
     if (batch == 0) return GBDPCG_OK;
     const unsigned long long items = (unsigned long long)batch * N;
     const unsigned long long sms = (unsigned long long)device_sms();
-    if (nx <= 32 && nu <= 32) {
+    const size_t staged_bytes = (size_t)8 * 2 * schur_recover_slice_elems<T>(nx, nu) * sizeof(T);
+    if (nx <= 32 && nu <= 32 && staged_bytes <= 96 * 1024) {
+        // one warp per (system, knot), the knot's matrices staged through the warp's slice of shared memory (two slices: next item in flight)
+        void (*fn)(const T *, const T *, const T *, const T *, const T *, const T *, const T *, T *, T *, uint32_t, uint32_t, uint32_t, uint32_t) =
+            schur_recover_staged_kernel<T, 0, 0>;
+        if (2 * nu == nx) {                                                    // (the usual shape: half as many inputs as states)
+            switch (nx) {
+#define CASE(NX) case NX: fn = schur_recover_staged_kernel<T, NX, NX / 2>; break;
+                GBDPCG_FOR_EACH_NX(CASE)
+#undef CASE
+                default: break;
+            }
+        }
+        int rc;
+        if ((rc = prepare_fn(reinterpret_cast<const void *>(fn), false))) return rc;
+        const unsigned long long per_sm = std::min<unsigned long long>(sizeof(T) == 4 ? 4 : 2, std::max<unsigned long long>(1, (200 * 1024) / (staged_bytes + 1024)));
+        const unsigned long long ctas = (items + 7) / 8;
+        const uint32_t grid = (uint32_t)std::min(ctas, sms * per_sm);
+        fn<<<grid, 256, staged_bytes, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);
+    } else if (nx <= 32 && nu <= 32) {
         const unsigned long long ctas = (items + 7) / 8;                       // one warp per (system, knot)
         const uint32_t grid = (uint32_t)(ctas < sms * 8 ? ctas : sms * 8);
         schur_recover_warp_kernel<T><<<grid, 256, 0, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);

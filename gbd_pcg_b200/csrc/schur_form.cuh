@@ -542,4 +542,157 @@ __global__ void __launch_bounds__(256) schur_recover_warp_kernel(const T *__rest
     }
 }
 
+// Staged form of the warp-per-(system, knot) recovery: the knot's four matrices reach the warp's own shared-memory slice by cp.async
+// (16-byte pieces where the source allows; every byte of Q^-1, R^-1, A, B is requested once, fully coalesced) and the NEXT item of the
+// warp is in flight while the current one is computed (two slices per warp).  A_k^T lambda reads the slice with a lane stride of nx
+// words, conflict-free for the even state sizes; the global-memory form above pays one L1 wavefront per 128-byte line of that stride.
+// Arithmetic and its order are those of schur_recover_warp_kernel (bit-identical results).
+template <typename T>
+__host__ __device__ inline uint32_t schur_recover_slice_elems(uint32_t nx, uint32_t nu)
+{
+    const uint32_t al = 16 / (uint32_t)sizeof(T);
+    auto up = [al](uint32_t n) { return (n + al - 1) / al * al; };
+    return 2 * up(nx * nx) + up(nx * nu) + up(nu * nu);
+}
+
+// COUNT > 0: the element count at compile time (loops unrolled).  PIECE = bytes per cp.async: the largest of 16 / 8 / sizeof(T) that
+// divides both the source address and COUNT * sizeof(T) when COUNT is known, else chosen from the address with an element-sized tail.
+template <typename T, int COUNT>
+__device__ __forceinline__ void warp_async_copy(T *dst, const T *src, int count, int lane)
+{
+    const uint32_t d0 = pv_smem_u32(dst);                        // 16-byte aligned by construction
+    const uintptr_t sa = reinterpret_cast<uintptr_t>(src);
+    const char *s0 = reinterpret_cast<const char *>(src);
+    if constexpr (COUNT > 0) {
+        constexpr int BYTES = COUNT * (int)sizeof(T);
+        if (BYTES % 16 == 0 && (sa & 15u) == 0) {
+#pragma unroll
+            for (int q0 = 0; q0 < BYTES / 16; q0 += 32) {
+                const int q = q0 + lane;
+                if (q < BYTES / 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 16u * (uint32_t)q), "l"(s0 + 16 * q) : "memory");
+            }
+        } else if (BYTES % 8 == 0 && (sa & 7u) == 0) {
+#pragma unroll
+            for (int q0 = 0; q0 < BYTES / 8; q0 += 32) {
+                const int q = q0 + lane;
+                if (q < BYTES / 8) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0 + 8u * (uint32_t)q), "l"(s0 + 8 * q) : "memory");
+            }
+        } else {
+#pragma unroll
+            for (int q0 = 0; q0 < COUNT; q0 += 32) {
+                const int q = q0 + lane;
+                if (q < COUNT) {
+                    if constexpr (sizeof(T) == 4)
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4u * (uint32_t)q), "l"(src + q) : "memory");
+                    else
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0 + 8u * (uint32_t)q), "l"(src + q) : "memory");
+                }
+            }
+        }
+    } else {
+        const int bytes = count * (int)sizeof(T);
+        int done = 0;
+        if ((sa & 15u) == 0) {
+            const int n16 = bytes / 16;
+            for (int q = lane; q < n16; q += 32)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d0 + 16u * (uint32_t)q), "l"(s0 + 16 * (size_t)q) : "memory");
+            done = n16 * 16;
+        } else if ((sa & 7u) == 0) {
+            const int n8 = bytes / 8;
+            for (int q = lane; q < n8; q += 32)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0 + 8u * (uint32_t)q), "l"(s0 + 8 * (size_t)q) : "memory");
+            done = n8 * 8;
+        }
+        for (int q = done / (int)sizeof(T) + lane; q < count; q += 32) {
+            if constexpr (sizeof(T) == 4)
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d0 + 4u * (uint32_t)q), "l"(src + q) : "memory");
+            else
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d0 + 8u * (uint32_t)q), "l"(src + q) : "memory");
+        }
+    }
+}
+
+// NX, NU > 0: state / input size at compile time (inner loops and the copy loops unrolled, immediate offsets -- the run-time form,
+// NX = NU = 0, is bound by instruction issue: 559 warp instructions per knot against ~250 here).
+template <typename T, int NX, int NU>
+__global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) schur_recover_staged_kernel(const T *__restrict__ Qinv, const T *__restrict__ Rinv,
+                                                                   const T *__restrict__ A, const T *__restrict__ B, const T *__restrict__ q,
+                                                                   const T *__restrict__ r, const T *__restrict__ lambda, T *__restrict__ x,
+                                                                   T *__restrict__ u, uint32_t nx_, uint32_t nu_, uint32_t N_, uint32_t batch)
+{
+    extern __shared__ __align__(16) unsigned char schur_smem_raw[];
+    const int nx = NX > 0 ? NX : (int)nx_, nu = NU > 0 ? NU : (int)nu_, N = (int)N_;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const uint32_t al = 16 / (uint32_t)sizeof(T);
+    const uint32_t e_bb = ((uint32_t)(nx * nx) + al - 1) / al * al, e_xu = ((uint32_t)(nx * nu) + al - 1) / al * al;
+    const uint32_t slice = schur_recover_slice_elems<T>((uint32_t)nx, (uint32_t)nu);
+    T *mine = reinterpret_cast<T *>(schur_smem_raw) + (size_t)wib * 2 * slice;
+    const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t items = batch * N_;
+    const int lx = lane < nx ? lane : 0, lu = lane < nu ? lane : 0;
+    // the item's matrices -> slice `buf` (asynchronous); its vector elements -> registers (used one loop trip later)
+    auto issue = [&](uint32_t item, int buf, T &ln, T &qk, T &rk) {
+        const uint32_t prob = item / N_;
+        const int k = (int)(item - prob * N_);
+        T *Qs = mine + (size_t)buf * slice, *As = Qs + e_bb, *Bs = As + e_bb, *Rs = Bs + e_xu;
+        warp_async_copy<T, NX * NX>(Qs, Qinv + (size_t)item * (nx * nx), nx * nx, lane);
+        const T *lam = lambda + (size_t)item * nx;
+        const bool has_next = k + 1 < N;
+        if (has_next) {
+            const size_t kk = (size_t)item - prob;                                            // prob * (N - 1) + k
+            warp_async_copy<T, NX * NX>(As, A + kk * (nx * nx), nx * nx, lane);
+            warp_async_copy<T, NX * NU>(Bs, B + kk * (nx * nu), nx * nu, lane);
+            warp_async_copy<T, NU * NU>(Rs, Rinv + kk * (nu * nu), nu * nu, lane);
+            rk = r[kk * nu + lu];
+            ln = lam[nx + lx];                                                                // lambda_{k+1}[lane]
+        } else {
+            rk = (T)0;
+            ln = (T)0;
+        }
+        qk = q[(size_t)item * nx + lx] + lam[lx];
+    };
+    uint32_t item = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int buf = 0;
+    T ln = (T)0, qk = (T)0, rk = (T)0;
+    if (item < items) issue(item, 0, ln, qk, rk);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (; item < items; item += warps, buf ^= 1) {
+        T ln_n = (T)0, qk_n = (T)0, rk_n = (T)0;
+        if (item + warps < items) issue(item + warps, buf ^ 1, ln_n, qk_n, rk_n);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const uint32_t prob = item / N_;
+        const int k = (int)(item - prob * N_);
+        const bool has_next = k + 1 < N;
+        asm volatile("cp.async.wait_group 1;" ::: "memory");      // this item's copies (the group before the one just committed)
+        __syncwarp();
+        const T *Qs = mine + (size_t)buf * slice, *As = Qs + e_bb, *Bs = As + e_bb, *Rs = Bs + e_xu;
+        T tx = (T)0, tu = (T)0;
+        if (has_next) {
+            T s = (T)0, s2 = (T)0;
+#pragma unroll
+            for (int p = 0; p < nx; p++) {
+                const T lp = __shfl_sync(0xffffffffu, ln, p);
+                s += As[lx * nx + p] * lp;                                                    // (A_k^T lambda_{k+1})[lane]
+                s2 += Bs[lu * nx + p] * lp;                                                   // (B_k^T lambda_{k+1})[lane]
+            }
+            tx = s; tu = s2;
+        }
+        tx = qk - tx;
+        tu = rk - tu;
+        T sx = (T)0;
+#pragma unroll
+        for (int p = 0; p < nx; p++) sx += Qs[p * nx + lx] * __shfl_sync(0xffffffffu, tx, p);
+        if (lane < nx) x[(size_t)item * nx + lane] = -sx;
+        if (has_next) {
+            T su = (T)0;
+#pragma unroll
+            for (int p = 0; p < nu; p++) su += Rs[p * nu + lu] * __shfl_sync(0xffffffffu, tu, p);
+            if (lane < nu) u[((size_t)item - prob) * nu + lane] = -su;
+        }
+        __syncwarp();                                             // the slice is free for the item after next
+        ln = ln_n; qk = qk_n; rk = rk_n;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
 }  // namespace gbdpcg
