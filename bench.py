@@ -189,6 +189,9 @@ def bind_to_gpu_numa(local):
 def timed_launches(torch, step, reset, steps, flush=None):
     """CUDA events on the launching stream around each step; `reset` (and the optional L2 flush) sit outside the event pair."""
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    # a ~1.5 ms spin kernel first: the host stays ahead of the device for the whole loop, so an event pair brackets the step's kernel(s) and
+    # not the host's launch latency (at 1,024 systems per GPU a step is ~96 us, the same order as one Python/ctypes call; time_single_solves does the same)
+    torch.cuda._sleep(3000000)
     for a, b in evs:
         reset()
         if flush is not None:
