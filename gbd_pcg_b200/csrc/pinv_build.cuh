@@ -25,6 +25,10 @@
 
 namespace gbdpcg {
 
+#ifndef PINV_L2_PREFETCH
+#define PINV_L2_PREFETCH 1
+#endif
+
 enum { PINV_IDENTITY = 0, PINV_JACOBI = 1, PINV_STAIR = 2 };
 
 struct PinvArgs {
@@ -275,6 +279,16 @@ __global__ void __launch_bounds__(256) pinv_build_kernel(const PinvArgs a)
                 }
                 pv_mbar_wait(mbar, phase);
                 phase ^= 1;
+#if PINV_L2_PREFETCH
+                // the image is rewritten in place, so the next item's copy cannot start before this item's store has read it: pull the
+                // next chunk of S into L2 meanwhile (its copy then waits on L2, not on HBM)
+                if (t == 32 && item + gridDim.x < items) {
+                    const uint32_t nitem = item + gridDim.x, nprob = nitem / a.nchunks;
+                    const int nk0 = (int)(nitem - nprob * a.nchunks) * chunk, ncnt = min(chunk, N - nk0);
+                    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(Sg + (size_t)nprob * a.mat_stride + (size_t)nk0 * BSZ),
+                                 "r"((uint32_t)(ncnt * BSZ * (int)sizeof(T))) : "memory");
+                }
+#endif
             } else {
                 copy_coalesced<T>(img, Sp + (size_t)k0 * BSZ, cnt * BSZ, true);
                 __syncthreads();
