@@ -429,8 +429,8 @@ static int make_plan(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &c
         Plan tp, rp;
         if (!(cfg.flags & auto_off) && !cfg.cluster && has_p && plan_fused_tmem64<T>(nx, N, has_p, cfg, &tp)) {
             const bool have_reg = plan_fused<T>(nx, N, has_p, cfg, batch, &rp);
-            // Beyond what a 16-CTA cluster of register rows holds, a 16-CTA cluster of this form still does (nx 14 fp32: N <= 1024 instead of 832,
-            // fp64 N <= 576 instead of 464): it goes before the cooperative grid -- nx 14 x N 800 fp32 single solve 148.8 -> 58.5 us.
+            // Beyond what a 16-CTA cluster of register rows holds, a 16-CTA cluster of this form still does (nx 14 fp32: N <= 1024 instead of 752,
+            // fp64 N <= 576 instead of 288): it goes before the cooperative grid -- nx 14 x N 800 fp32 single solve 148.8 -> 58.5 us.
             if (!have_reg) {
                 *out = tp;
                 return GBDPCG_OK;

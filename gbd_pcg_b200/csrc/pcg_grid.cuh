@@ -1,7 +1,7 @@
 // pcg_grid.cuh -- systems LARGER than one 16-CTA cluster: a cooperative grid of register-row CTAs owns one system.
 //
-// The cluster kernel (pcg_fused.cuh) holds a system inside one thread-block cluster: at most 16 CTAs, i.e. N <= 832 knot points for
-// nx = 14 in fp32.  The reference has no such limit -- its kernel is one CTA per knot point on a cooperative grid and runs any N
+// The cluster kernel (pcg_fused.cuh) holds a system inside one thread-block cluster: at most 16 CTAs, i.e. N <= 752 knot points for
+// nx = 14 in fp32 with register rows, 1024 with Phi^-1 in tensor memory.  The reference has no such limit -- its kernel is one CTA per knot point on a cooperative grid and runs any N
 // whose N CTAs are co-resident (reference include/pcg.cuh:23-49, launch at include/interface.cuh:130-132), 4 grid.sync per
 // iteration with every vector exchanged through global memory (include/pcg.cuh:154-208).  This kernel covers that range:
 //   * cooperative launch of G CTAs (one per SM at most), CTA c owns bpc consecutive block-rows, a thread owns R rows of S and
