@@ -1157,7 +1157,9 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
     const unsigned long long items = (unsigned long long)batch * N;
     const unsigned long long sms = (unsigned long long)device_sms();
     const size_t staged_bytes = (size_t)8 * 2 * schur_recover_slice_elems<T>(nx, nu) * sizeof(T);
-    if (nx <= 32 && nu <= 32 && staged_bytes <= 96 * 1024) {
+    const char *env_rec = getenv("GBDPCG_RECOVER_GLOBAL");                     // A/B knob: the global-memory form of the warp kernel
+    const bool staged = !(env_rec && atoi(env_rec));
+    if (nx <= 32 && nu <= 32 && staged_bytes <= 96 * 1024 && staged) {
         // one warp per (system, knot), the knot's matrices staged through the warp's slice of shared memory (two slices: next item in flight)
         void (*fn)(const T *, const T *, const T *, const T *, const T *, const T *, const T *, T *, T *, uint32_t, uint32_t, uint32_t, uint32_t) =
             schur_recover_staged_kernel<T, 0, 0>;

@@ -120,3 +120,27 @@ def test_reference_example_matrix_from_its_stage_data():
         g.schur_form_dev(nx, nu, N, 1, dd["Q"], dd["R"], dd["A"], dd["B"], dd["q"], dd["r"], dd["c"], S, gam)
         torch.cuda.synchronize()
         assert np.abs(S.cpu().numpy().astype(np.float64) - g.synth.EXAMPLE_S).max() < 6e-5
+
+
+@pytest.mark.parametrize("dt", [np.float32, np.float64])
+@pytest.mark.parametrize("nx,nu,N,batch", [(14, 7, 32, 40), (12, 4, 33, 7), (2, 1, 3, 5), (7, 3, 9, 3), (16, 8, 17, 2), (16, 16, 6, 3)])
+def test_staged_recovery_equals_the_global_memory_form_bit_for_bit(nx, nu, N, batch, dt, monkeypatch):
+    """The staged recovery kernel (matrices through per-warp shared-memory slices, next knot in flight; sizes at compile time where
+    nu = nx/2) keeps the arithmetic and its order: x, u equal those of the global-memory warp kernel bit for bit
+    (GBDPCG_RECOVER_GLOBAL=1 selects that one).  Odd pointers' alignment classes are all met: knot strides of 196 / 98 / 49 elements."""
+    torch = _torch()
+    rng = np.random.default_rng(5)
+    mk = lambda *shape: torch.from_numpy(rng.standard_normal(shape).astype(dt)).cuda()
+    Qi, Ri = mk(batch * N * nx * nx), mk(batch * (N - 1) * nu * nu)
+    A, B = mk(batch * (N - 1) * nx * nx), mk(batch * (N - 1) * nx * nu)
+    q, r, lam = mk(batch * N * nx), mk(batch * (N - 1) * nu), mk(batch * N * nx)
+    outs = []
+    for env in ("0", "1"):
+        monkeypatch.setenv("GBDPCG_RECOVER_GLOBAL", env)
+        x = torch.full((batch * N * nx,), float("nan"), dtype=Qi.dtype, device="cuda")
+        u = torch.full((batch * (N - 1) * nu,), float("nan"), dtype=Qi.dtype, device="cuda")
+        g.schur_recover_dev(nx, nu, N, batch, Qi, Ri, A, B, q, r, lam, x, u)
+        torch.cuda.synchronize()
+        outs.append((x.cpu().numpy(), u.cpu().numpy()))
+    assert np.isfinite(outs[0][0]).all() and np.isfinite(outs[0][1]).all()
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
