@@ -63,6 +63,7 @@ struct Plan {
     bool generic = false;
     bool fused_kernel = false;        // second-generation kernel (pcg_fused.cuh)
     bool tmem_kernel = false;         // tensor-memory batched kernel (pcg_tmem.cuh / pcg_tmem4.cuh)
+    bool grid_one_barrier = false;    // ... its one-barrier form (pcg_grid1_kernel: other scratch layout, 2 TPB ghost-row threads)
     bool grid_kernel = false;         // cooperative-grid kernel for systems beyond one cluster (pcg_grid.cuh); `cluster` = CTAs of the grid
     int tmem_per_sm = 0;              // CTAs of it that share an SM (tensor-memory columns, registers)
     int rpt = 1, fused = 0;           // rows per thread, single-reduction recurrence
@@ -248,7 +249,7 @@ static bool plan_fused_tmem64(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_
 // Systems too large for one 16-CTA cluster: a cooperative grid of register-row CTAs, at most one per SM (pcg_grid.cuh).
 // The reference runs any N whose N CTAs are co-resident (include/pcg.cuh:23-49); this covers N up to SMs x block-rows per CTA.
 template <typename T>
-static bool plan_grid(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out)
+static bool plan_grid(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &cfg, Plan *out, bool allow_one_barrier = true)
 {
     constexpr bool f64 = sizeof(T) == 8;
     if (cfg.flags & (GBDPCG_FLAG_TEXTBOOK)) return false;      // single-reduction recurrence only
@@ -284,6 +285,16 @@ static bool plan_grid(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
             out->cluster = G; out->bpc = bpc; out->threads = round_up(bpc * tpb, 32); out->nbuf = 1; out->pmode = v->pmode;
             out->smem = make_grid_plan<T>((int)nx, v->nxp, bpc, v->pmode).total; out->fn = v->fn; out->name = v->name; out->rpt = v->rpt;
             out->fused = 1;
+            out->grid_one_barrier = false;
+            // One barrier per iteration (pcg_grid1_kernel) where every CTA owns at least two block-rows and the CTA has room for the
+            // 2 x tpb ghost-row threads: 5.2 -> see DESIGN 3.9 us per iteration.  GBDPCG_GRID_TWO_BARRIERS=1: A/B knob.
+            const int threads1 = round_up(bpc * tpb + 2 * tpb, 32);
+            const size_t smem1 = make_grid1_plan<T>((int)nx, v->nxp, bpc, v->pmode).total;
+            if (allow_one_barrier && bpc >= 2 && G >= 2 && threads1 <= v->maxt && threads1 >= 4 * (int)nx && smem1 <= kMaxDynSmem &&
+                !getenv("GBDPCG_GRID_TWO_BARRIERS")) {
+                out->grid_one_barrier = true;
+                out->threads = threads1; out->smem = smem1; out->fn = v->fn1; out->name = v->name1;
+            }
             return true;
         }
     return false;
@@ -675,7 +686,8 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
         T *scratch = nullptr;
         cudaMemPool_t pool;
         if ((rc = scratch_pool(&pool))) return rc;
-        CK(cudaMallocFromPoolAsync((void **)&scratch, grid_scratch_elems<T>((int)nx, G) * sizeof(T), pool, stream));
+        const size_t selems = p.grid_one_barrier ? grid1_scratch_elems<T>((int)nx, G) : grid_scratch_elems<T>((int)nx, G);
+        CK(cudaMallocFromPoolAsync((void **)&scratch, selems * sizeof(T), pool, stream));
         GridScratch<T> gs;
         gs.halo_r = scratch; gs.halo_rt = scratch + (size_t)G * 2 * nx; gs.halo_w = scratch + (size_t)G * 4 * nx;
         gs.partials = scratch + (size_t)G * 6 * nx;
@@ -689,7 +701,8 @@ static int launch(const Plan &p, const T *S, const T *P, const T *gamma, T *lamb
         at[0].val.cooperative = 1;
         lc.attrs = at; lc.numAttrs = 1;
         void *args[] = {&a, &gs};
-        const cudaError_t e = cudaLaunchKernelExC(&lc, p.fn, args);
+        void *args1[] = {&a, &scratch};
+        const cudaError_t e = cudaLaunchKernelExC(&lc, p.fn, p.grid_one_barrier ? args1 : args);
         cudaFreeAsync(scratch, stream);
         if (e != cudaSuccess) return fail_cuda(e, "cudaLaunchKernelExC (cooperative grid)", __LINE__);
         g_launches.fetch_add(1, std::memory_order_relaxed);
@@ -1354,7 +1367,7 @@ static int solve_dev_static_scratch(const T *S, const T *Pinv, const T *gamma, T
     if (rc) return rc;
     const bool has_p = use_pinv(Pinv, cfg);
     Plan p;
-    if (!plan_grid<T>(nx, N, has_p, *cfg, &p))
+    if (!plan_grid<T>(nx, N, has_p, *cfg, &p, /*allow_one_barrier=*/false))       // (the two-barrier form: its scratch is what the static array was sized for)
         return fail(GBDPCG_ERR_UNSUPPORTED, "no cooperative-grid kernel for nx=%u N=%u %s flags=0x%x cluster=%u (even nx <= 16, default recurrence, "
                     "cluster = 0, N within the co-residency limit)", nx, N, sizeof(T) == 8 ? "f64" : "f32", cfg->flags, cfg->cluster);
     const int G = p.cluster;

@@ -85,6 +85,8 @@ struct GridVariant {
     int nxp;
     const void *fn;
     const char *name;
+    const void *fn1;          // pcg_grid1_kernel: one grid barrier per iteration (ghost rows of Phi^-1)
+    const char *name1;
 };
 #define GBDPCG_DECLARE_GRID(NX)                              \
     const GridVariant *grid_variants_f32_##NX(int *count);   \

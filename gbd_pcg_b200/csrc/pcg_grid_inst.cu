@@ -53,7 +53,9 @@ constexpr int MAXT_2K = MAXT_2 > 0 ? MAXT_2 : 32;
 
 #define VARIANT(PM, MT)                                                                           \
     {NX, INST_F64, RPT, PM, MT, Geo<InstT>::nxp(NX), (const void *)pcg_grid_kernel<InstT, NX, RPT, PM, MT>, \
-     "pcg_grid<" INST_DT ",nx=" STR(INST_NX) ",R=" STR(INST_RPT) "," #PM ">"}
+     "pcg_grid<" INST_DT ",nx=" STR(INST_NX) ",R=" STR(INST_RPT) "," #PM ">",                               \
+     (const void *)pcg_grid1_kernel<InstT, NX, RPT, PM, MT>,                                                \
+     "pcg_grid1<" INST_DT ",nx=" STR(INST_NX) ",R=" STR(INST_RPT) "," #PM ",one barrier>"}
 
 static const GridVariant g_table[] = {VARIANT(P_NONE, MAXT_1), VARIANT(P_SMEM, MAXT_1), VARIANT(P_REG, MAXT_2K)};
 

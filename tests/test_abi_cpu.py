@@ -93,6 +93,20 @@ def test_plan_query_tensor_memory_cluster_before_the_grid(nx, N, dtype):
     assert "pcg_grid" in g.plan_query(nx, N, dtype, True, g.pcg_config(empty_pinv=0, flags=_lib.FLAG_NO_TMEM))["kernel"]
 
 
+def test_plan_query_one_barrier_form_of_the_grid_kernel(monkeypatch):
+    """Beyond one cluster the planner takes the one-barrier form of the cooperative-grid kernel (ghost rows of Phi^-1: 2 x nx/R threads
+    beyond the owners') wherever every CTA owns two block-rows and the CTA has room for those threads; the largest systems (CTAs
+    already at their register budget's thread count) and GBDPCG_GRID_TWO_BARRIERS=1 keep the two-barrier form."""
+    for nx, N, dtype in [(14, 1500, np.float32), (14, 1000, np.float64), (8, 2500, np.float64), (6, 6000, np.float32)]:
+        info = g.plan_query(nx, N, dtype, True)
+        assert "pcg_grid1" in info["kernel"] and "one barrier" in info["kernel"]
+        rpt = 1 if dtype == np.float64 else 2
+        assert info["threads"] >= info["block_rows"] * (nx // rpt) + 2 * (nx // rpt) and info["block_rows"] >= 2
+    assert "pcg_grid<" in g.plan_query(14, 5328, np.float32, True)["kernel"]
+    monkeypatch.setenv("GBDPCG_GRID_TWO_BARRIERS", "1")
+    assert "pcg_grid<" in g.plan_query(14, 1500, np.float32, True)["kernel"]
+
+
 def test_plan_query_rejects_what_cannot_fit():
     with pytest.raises(g.GbdpcgError) as e:
         g.plan_query(14, 4096, np.float64, True)
