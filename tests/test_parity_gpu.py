@@ -232,6 +232,31 @@ def test_systems_beyond_one_cluster(nx, nu, N, dt, precond):
     assert it2 == it and np.array_equal(lam2, lam)
 
 
+@pytest.mark.parametrize("nx,nu,N,dt", [(14, 7, 1031, np.float32), (14, 7, 1032, np.float32), (14, 7, 1033, np.float32),
+                                         (10, 5, 820, np.float64), (10, 5, 821, np.float64), (8, 4, 3004, np.float32)])
+@pytest.mark.parametrize("precond", ["stair", "jacobi"])
+def test_one_barrier_grid_kernel_short_last_cta(nx, nu, N, dt, precond, monkeypatch):
+    """pcg_grid1_kernel (one grid barrier per iteration: ghost rows of Phi^-1, ghosts of r and s two block-rows deep) where the last CTA
+    owns only 1, 2 or 3 block-rows -- the second-level ghost of its left neighbour then does not exist or is the system's last row:
+    against the oracle at the suite's bar, and bit for bit against the two-barrier form (GBDPCG_GRID_TWO_BARRIERS=1)."""
+    tol = 1e-6 if dt == np.float32 else 1e-10
+    S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 5000), precond, seed=4)
+    cfg = g.pcg_config(empty_pinv=0 if P is not None else 1)
+    info = g.plan_query(nx, N, dt, P is not None, cfg)
+    assert "pcg_grid1" in info["kernel"] and N - (info["cluster"] - 1) * info["block_rows"] in (1, 2, 3)
+    lam0 = np.random.default_rng(1).standard_normal(N * nx).astype(dt) * 0.01
+    lam, it, ex = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
+    assert not ex
+    lam_o, it_o, _ = oracle.pcg(S, P, gam, lam0, nx, N, tol, max_iter, order=0)
+    assert abs(it - it_o) <= 1, (it, it_o)
+    lam_eq = lam_o if it == it_o else oracle.pcg(S, P, gam, lam0, nx, N, 0.0, it, order=0)[0]
+    assert rel_err(lam, lam_eq) <= LAMBDA_TOL[np.dtype(dt)], (rel_err(lam, lam_eq), it, it_o)
+    monkeypatch.setenv("GBDPCG_GRID_TWO_BARRIERS", "1")
+    assert "pcg_grid<" in g.plan_query(nx, N, dt, P is not None, cfg)["kernel"]
+    lam2, it2, ex2 = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
+    assert it2 == it and not ex2 and np.array_equal(lam2, lam)
+
+
 def test_grid_kernel_semantics_and_batch():
     """max_iter = 0 leaves lambda; a low cap reports the flag; warm start; a batch of large systems (solved one after the other on
     the same cooperative grid) equals the single solves; NaN-poisoned padding blocks never reach the arithmetic."""
