@@ -1367,11 +1367,16 @@ static int solve_dev_static_scratch(const T *S, const T *Pinv, const T *gamma, T
     if (rc) return rc;
     const bool has_p = use_pinv(Pinv, cfg);
     Plan p;
-    if (!plan_grid<T>(nx, N, has_p, *cfg, &p, /*allow_one_barrier=*/false))       // (the two-barrier form: its scratch is what the static array was sized for)
+    // The one-barrier form where its (larger, parity-alternating) exchange buffers fit the static array, else the two-barrier form the
+    // array was sized for: the size limit documented in gbdpcg.h -- CTAs * (6 nx + 2) * sizeof(T) -- is unchanged, results are bit-identical.
+    bool planned = plan_grid<T>(nx, N, has_p, *cfg, &p, /*allow_one_barrier=*/true);
+    if (planned && p.grid_one_barrier && grid1_scratch_elems<T>((int)nx, p.cluster) * sizeof(T) > (size_t)GBDPCG_STATIC_SCRATCH_BYTES)
+        planned = plan_grid<T>(nx, N, has_p, *cfg, &p, /*allow_one_barrier=*/false);
+    if (!planned)
         return fail(GBDPCG_ERR_UNSUPPORTED, "no cooperative-grid kernel for nx=%u N=%u %s flags=0x%x cluster=%u (even nx <= 16, default recurrence, "
                     "cluster = 0, N within the co-residency limit)", nx, N, sizeof(T) == 8 ? "f64" : "f32", cfg->flags, cfg->cluster);
     const int G = p.cluster;
-    const size_t need = grid_scratch_elems<T>((int)nx, G) * sizeof(T);
+    const size_t need = (p.grid_one_barrier ? grid1_scratch_elems<T>((int)nx, G) : grid_scratch_elems<T>((int)nx, G)) * sizeof(T);
     if (need > (size_t)GBDPCG_STATIC_SCRATCH_BYTES)
         return fail(GBDPCG_ERR_UNSUPPORTED, "nx=%u N=%u on %d CTAs needs %zu bytes of exchange scratch; the static array holds %d "
                     "(GBDPCG_STATIC_SCRATCH_BYTES) -- use gbdpcg_solve_dev_*", nx, N, G, need, (int)GBDPCG_STATIC_SCRATCH_BYTES);
@@ -1401,7 +1406,8 @@ static int solve_dev_static_scratch(const T *S, const T *Pinv, const T *gamma, T
     at[0].val.cooperative = 1;
     lc.attrs = at; lc.numAttrs = 1;
     void *args[] = {&a, &gs};
-    const cudaError_t e = cudaLaunchKernelExC(&lc, p.fn, args);
+    void *args1[] = {&a, &scratch};
+    const cudaError_t e = cudaLaunchKernelExC(&lc, p.fn, p.grid_one_barrier ? args1 : args);
     if (e != cudaSuccess) return fail_cuda(e, "cudaLaunchKernelExC (cooperative grid, static scratch)", __LINE__);
     g_launches.fetch_add(1, std::memory_order_relaxed);
     return GBDPCG_OK;
