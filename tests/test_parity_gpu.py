@@ -257,6 +257,38 @@ def test_one_barrier_grid_kernel_short_last_cta(nx, nu, N, dt, precond, monkeypa
     assert it2 == it and not ex2 and np.array_equal(lam2, lam)
 
 
+@pytest.mark.parametrize("nx,nu,N,dt", [(14, 7, 1500, np.float32), (16, 8, 1000, np.float64), (10, 5, 2000, np.float64)])
+def test_one_barrier_grid_kernel_pinv_in_shared_memory(nx, nu, N, dt, monkeypatch):
+    """pcg_grid1_kernel with Phi^-1 in shared memory (GBDPCG_FLAG_PINV_SMEM; the planner's own choice where two matrices do not fit the
+    register file, e.g. fp64 nx = 16): the ghost rows read their neighbour's block-row from the CTA's own image.  Oracle parity and
+    bit-identity with the two-barrier form."""
+    tol = 1e-6 if dt == np.float32 else 1e-10
+    S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 5000), "stair", seed=6)
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0, flags=g._lib.FLAG_PINV_SMEM)
+    lam0 = np.zeros(N * nx, dtype=dt)
+
+    def run():
+        torch = _torch()
+        d_S, d_P, d_g, d_l = (torch.from_numpy(a).cuda() for a in (S, P, gam, lam0.copy()))
+        d_it = torch.zeros(1, dtype=torch.int32, device="cuda")
+        g.solve_dev_async(nx, N, d_S, d_P, d_g, d_l, cfg, d_it, None)
+        torch.cuda.synchronize()
+        return d_l.cpu().numpy(), int(d_it.item())
+
+    k1 = g.plan_query(nx, N, dt, True, cfg)["kernel"]
+    assert "pcg_grid1" in k1 and "P_SMEM" in k1
+    lam, it = run()
+    lam_o, it_o, _ = oracle.pcg(S, P, gam, lam0, nx, N, tol, max_iter, order=0)
+    assert abs(it - it_o) <= 1
+    lam_eq = lam_o if it == it_o else oracle.pcg(S, P, gam, lam0, nx, N, 0.0, it, order=0)[0]
+    assert rel_err(lam, lam_eq) <= LAMBDA_TOL[np.dtype(dt)]
+    monkeypatch.setenv("GBDPCG_GRID_TWO_BARRIERS", "1")
+    k2 = g.plan_query(nx, N, dt, True, cfg)["kernel"]
+    assert "pcg_grid<" in k2 and "P_SMEM" in k2
+    lam2, it2 = run()
+    assert it2 == it and np.array_equal(lam2, lam)
+
+
 def test_grid_kernel_semantics_and_batch():
     """max_iter = 0 leaves lambda; a low cap reports the flag; warm start; a batch of large systems (solved one after the other on
     the same cooperative grid) equals the single solves; NaN-poisoned padding blocks never reach the arithmetic."""
