@@ -280,20 +280,29 @@ static bool plan_grid(uint32_t nx, uint32_t N, bool has_p, const gbdpcg_config &
             const int bpc_2warps = (64 + tpb - 1) / tpb;           // ... but a CTA keeps at least two warps
             if (bpc < bpc_2warps) bpc = bpc_2warps;
             if (bpc > bpc_max) continue;
+            // One barrier per iteration (pcg_grid1_kernel) where every CTA owns at least two block-rows and the CTA has room for the
+            // 2 x tpb ghost-row threads.  GBDPCG_GRID_TWO_BARRIERS=1: A/B knob.
+            auto one_barrier_fits = [&](int bb) {
+                const int g1 = ((int)N + bb - 1) / bb, th1 = round_up(bb * tpb + 2 * tpb, 32);
+                return allow_one_barrier && bb >= 2 && g1 >= 2 && th1 <= v->maxt && th1 >= 4 * (int)nx &&
+                       make_grid1_plan<T>((int)nx, v->nxp, bb, v->pmode).total <= kMaxDynSmem && !getenv("GBDPCG_GRID_TWO_BARRIERS");
+            };
+            // ... and with one barrier HALF as many CTAs of twice the size are faster still where they fit (the barrier's arrivals are
+            // serialised on one L2 line: nx 14 N 1500 fp32 126 -> 118 us on 69 CTAs, fp64 N 1000 184 -> 171 on 72; a third as many: 128).
+            // GBDPCG_GRID_BPC_SCALE=1 keeps one CTA per SM (A/B knob).
+            int scale = 2;
+            if (const char *e = getenv("GBDPCG_GRID_BPC_SCALE")) { const int sc = atoi(e); if (sc >= 1 && sc <= 8) scale = sc; }
+            if (scale > 1 && ((int)N + bpc - 1) / bpc > sms / 2 && bpc * scale <= bpc_max && one_barrier_fits(bpc * scale)) bpc *= scale;
             const int G = ((int)N + bpc - 1) / bpc;
             out->generic = false; out->fused_kernel = false; out->tmem_kernel = false; out->grid_kernel = true; out->v = nullptr;
             out->cluster = G; out->bpc = bpc; out->threads = round_up(bpc * tpb, 32); out->nbuf = 1; out->pmode = v->pmode;
             out->smem = make_grid_plan<T>((int)nx, v->nxp, bpc, v->pmode).total; out->fn = v->fn; out->name = v->name; out->rpt = v->rpt;
             out->fused = 1;
             out->grid_one_barrier = false;
-            // One barrier per iteration (pcg_grid1_kernel) where every CTA owns at least two block-rows and the CTA has room for the
-            // 2 x tpb ghost-row threads: 5.2 -> see DESIGN 3.9 us per iteration.  GBDPCG_GRID_TWO_BARRIERS=1: A/B knob.
-            const int threads1 = round_up(bpc * tpb + 2 * tpb, 32);
-            const size_t smem1 = make_grid1_plan<T>((int)nx, v->nxp, bpc, v->pmode).total;
-            if (allow_one_barrier && bpc >= 2 && G >= 2 && threads1 <= v->maxt && threads1 >= 4 * (int)nx && smem1 <= kMaxDynSmem &&
-                !getenv("GBDPCG_GRID_TWO_BARRIERS")) {
+            if (one_barrier_fits(bpc)) {
                 out->grid_one_barrier = true;
-                out->threads = threads1; out->smem = smem1; out->fn = v->fn1; out->name = v->name1;
+                out->threads = round_up(bpc * tpb + 2 * tpb, 32);
+                out->smem = make_grid1_plan<T>((int)nx, v->nxp, bpc, v->pmode).total; out->fn = v->fn1; out->name = v->name1;
             }
             return true;
         }

@@ -1,5 +1,6 @@
 """Cooperative-grid kernel, one-barrier form with Phi^-1 in registers / in shared memory (GBDPCG_FLAG_PINV_SMEM) and the two-barrier form\n(GBDPCG_GRID_TWO_BARRIERS=1) on the same systems: kernels, iteration counts, error against the oracle, bit-identity.   usage: python scripts/check_grid_forms.py"""
 import os, sys, numpy as np
+os.environ.setdefault("GBDPCG_GRID_BPC_SCALE", "1")   # one CTA per SM in both forms: the same decomposition, so the results can be compared bit for bit
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 import gbd_pcg_b200 as g
 from gbd_pcg_b200 import _lib

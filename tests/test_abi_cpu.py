@@ -103,6 +103,12 @@ def test_plan_query_one_barrier_form_of_the_grid_kernel(monkeypatch):
         rpt = 1 if dtype == np.float64 else 2
         assert info["threads"] >= info["block_rows"] * (nx // rpt) + 2 * (nx // rpt) and info["block_rows"] >= 2
     assert "pcg_grid<" in g.plan_query(14, 5328, np.float32, True)["kernel"]
+    # with one barrier, half as many CTAs of twice the size where they fit (the arrivals of a barrier are serialised)
+    half, full = g.plan_query(14, 1500, np.float32, True), None
+    monkeypatch.setenv("GBDPCG_GRID_BPC_SCALE", "1")
+    full = g.plan_query(14, 1500, np.float32, True)
+    assert half["block_rows"] == 2 * full["block_rows"] and half["cluster"] <= 74 < full["cluster"]
+    monkeypatch.delenv("GBDPCG_GRID_BPC_SCALE")
     monkeypatch.setenv("GBDPCG_GRID_TWO_BARRIERS", "1")
     assert "pcg_grid<" in g.plan_query(14, 1500, np.float32, True)["kernel"]
 

@@ -232,13 +232,18 @@ def test_systems_beyond_one_cluster(nx, nu, N, dt, precond):
     assert it2 == it and np.array_equal(lam2, lam)
 
 
-@pytest.mark.parametrize("nx,nu,N,dt", [(14, 7, 1031, np.float32), (14, 7, 1032, np.float32), (14, 7, 1033, np.float32),
-                                         (10, 5, 820, np.float64), (10, 5, 821, np.float64), (8, 4, 3004, np.float32)])
+@pytest.mark.parametrize("scale,nx,nu,N,dt", [(1, 14, 7, 1031, np.float32), (1, 14, 7, 1032, np.float32), (1, 14, 7, 1033, np.float32),
+                                               (1, 10, 5, 820, np.float64), (1, 10, 5, 821, np.float64), (1, 8, 4, 3004, np.float32),
+                                               (2, 14, 7, 1041, np.float32), (2, 14, 7, 1042, np.float32), (2, 14, 7, 1043, np.float32),
+                                               (2, 10, 5, 827, np.float64), (2, 10, 5, 828, np.float64), (2, 8, 4, 3025, np.float32)])
 @pytest.mark.parametrize("precond", ["stair", "jacobi"])
-def test_one_barrier_grid_kernel_short_last_cta(nx, nu, N, dt, precond, monkeypatch):
+def test_one_barrier_grid_kernel_short_last_cta(scale, nx, nu, N, dt, precond, monkeypatch):
     """pcg_grid1_kernel (one grid barrier per iteration: ghost rows of Phi^-1, ghosts of r and s two block-rows deep) where the last CTA
     owns only 1, 2 or 3 block-rows -- the second-level ghost of its left neighbour then does not exist or is the system's last row:
-    against the oracle at the suite's bar, and bit for bit against the two-barrier form (GBDPCG_GRID_TWO_BARRIERS=1)."""
+    against the oracle at the suite's bar, and bit for bit against the two-barrier form (GBDPCG_GRID_TWO_BARRIERS=1) where that runs the
+    same decomposition: scale 1 = one CTA per SM (GBDPCG_GRID_BPC_SCALE=1); scale 2 = the planner's default for this form, half as many
+    CTAs of twice the size, which the two-barrier form does not take."""
+    monkeypatch.setenv("GBDPCG_GRID_BPC_SCALE", str(scale))
     tol = 1e-6 if dt == np.float32 else 1e-10
     S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 5000), precond, seed=4)
     cfg = g.pcg_config(empty_pinv=0 if P is not None else 1)
@@ -254,7 +259,9 @@ def test_one_barrier_grid_kernel_short_last_cta(nx, nu, N, dt, precond, monkeypa
     monkeypatch.setenv("GBDPCG_GRID_TWO_BARRIERS", "1")
     assert "pcg_grid<" in g.plan_query(nx, N, dt, P is not None, cfg)["kernel"]
     lam2, it2, ex2 = gpu_solve(S, P, gam, lam0, nx, N, tol, max_iter)
-    assert it2 == it and not ex2 and np.array_equal(lam2, lam)
+    assert not ex2 and abs(it2 - it) <= (0 if scale == 1 else 1)
+    if scale == 1:
+        assert np.array_equal(lam2, lam)
 
 
 @pytest.mark.parametrize("nx,nu,N,dt", [(14, 7, 1500, np.float32), (16, 8, 1000, np.float64), (10, 5, 2000, np.float64)])
@@ -262,6 +269,7 @@ def test_one_barrier_grid_kernel_pinv_in_shared_memory(nx, nu, N, dt, monkeypatc
     """pcg_grid1_kernel with Phi^-1 in shared memory (GBDPCG_FLAG_PINV_SMEM; the planner's own choice where two matrices do not fit the
     register file, e.g. fp64 nx = 16): the ghost rows read their neighbour's block-row from the CTA's own image.  Oracle parity and
     bit-identity with the two-barrier form."""
+    monkeypatch.setenv("GBDPCG_GRID_BPC_SCALE", "1")       # (the two-barrier form keeps one CTA per SM: compare the same decomposition)
     tol = 1e-6 if dt == np.float32 else 1e-10
     S, P, gam, nx, N, tol, max_iter = make_system((nx, nu, N, dt, tol, 5000), "stair", seed=6)
     cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=max_iter, empty_pinv=0, flags=g._lib.FLAG_PINV_SMEM)
