@@ -1178,7 +1178,7 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
     if (batch == 0) return GBDPCG_OK;
     const unsigned long long items = (unsigned long long)batch * N;
     const unsigned long long sms = (unsigned long long)device_sms();
-    const size_t staged_bytes = (size_t)8 * 2 * schur_recover_slice_elems<T>(nx, nu) * sizeof(T);
+    const size_t staged_bytes = (size_t)8 * 3 * schur_recover_slice_elems<T>(nx, nu) * sizeof(T);
     const char *env_rec = getenv("GBDPCG_RECOVER_GLOBAL");                     // A/B knob: the global-memory form of the warp kernel
     const bool staged = !(env_rec && atoi(env_rec));
     if (nx <= 32 && nu <= 32 && staged_bytes <= 96 * 1024 && staged) {
@@ -1195,7 +1195,7 @@ static int schur_recover_dev(const T *Qinv, const T *Rinv, const T *A, const T *
         }
         int rc;
         if ((rc = prepare_fn(reinterpret_cast<const void *>(fn), false))) return rc;
-        const unsigned long long per_sm = std::min<unsigned long long>(sizeof(T) == 4 ? 4 : 2, std::max<unsigned long long>(1, (200 * 1024) / (staged_bytes + 1024)));
+        const unsigned long long per_sm = std::min<unsigned long long>(sizeof(T) == 4 ? 4 : 2, std::max<unsigned long long>(1, (227 * 1024) / (staged_bytes + 1024)));
         const unsigned long long ctas = (items + 7) / 8;
         const uint32_t grid = (uint32_t)std::min(ctas, sms * per_sm);
         fn<<<grid, 256, staged_bytes, st>>>(Qinv, Rinv, A, B, q, r, lambda, x, u, nx, nu, N, batch);

@@ -543,8 +543,8 @@ __global__ void __launch_bounds__(256) schur_recover_warp_kernel(const T *__rest
 }
 
 // Staged form of the warp-per-(system, knot) recovery: the knot's four matrices reach the warp's own shared-memory slice by cp.async
-// (16-byte pieces where the source allows; every byte of Q^-1, R^-1, A, B is requested once, fully coalesced) and the NEXT item of the
-// warp is in flight while the current one is computed (two slices per warp).  A_k^T lambda reads the slice with a lane stride of nx
+// (16-byte pieces where the source allows; every byte of Q^-1, R^-1, A, B is requested once, fully coalesced) and the NEXT TWO items of the
+// warp are in flight while the current one is computed (three slices per warp).  A_k^T lambda reads the slice with a lane stride of nx
 // words, conflict-free for the even state sizes; the global-memory form above pays one L1 wavefront per 128-byte line of that stride.
 // Arithmetic and its order are those of schur_recover_warp_kernel (bit-identical results).
 template <typename T>
@@ -626,12 +626,12 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) schur_recover_s
     const uint32_t al = 16 / (uint32_t)sizeof(T);
     const uint32_t e_bb = ((uint32_t)(nx * nx) + al - 1) / al * al, e_xu = ((uint32_t)(nx * nu) + al - 1) / al * al;
     const uint32_t slice = schur_recover_slice_elems<T>((uint32_t)nx, (uint32_t)nu);
-    T *mine = reinterpret_cast<T *>(schur_smem_raw) + (size_t)wib * 2 * slice;
+    T *mine = reinterpret_cast<T *>(schur_smem_raw) + (size_t)wib * 3 * slice;
     const uint32_t warps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t items = batch * N_;
     const int lx = lane < nx ? lane : 0, lu = lane < nu ? lane : 0;
     // the item's matrices -> slice `buf` (asynchronous); its vector elements -> registers (used one loop trip later)
-    auto issue = [&](uint32_t item, int buf, T &ln, T &qk, T &rk) {
+    auto issue = [&](uint32_t item, int buf, T &ln, T &qk, T &lk, T &rk) {
         const uint32_t prob = item / N_;
         const int k = (int)(item - prob * N_);
         T *Qs = mine + (size_t)buf * slice, *As = Qs + e_bb, *Bs = As + e_bb, *Rs = Bs + e_xu;
@@ -649,21 +649,27 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) schur_recover_s
             rk = (T)0;
             ln = (T)0;
         }
-        qk = q[(size_t)item * nx + lx] + lam[lx];
+        qk = q[(size_t)item * nx + lx];                   // (q_k and lambda_k are added when they are USED: an add here would wait for both loads)
+        lk = lam[lx];
     };
     uint32_t item = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int buf = 0;
-    T ln = (T)0, qk = (T)0, rk = (T)0;
-    if (item < items) issue(item, 0, ln, qk, rk);
+    // three slices per warp: the item being computed and the next TWO in flight (one ahead left the warp waiting on HBM for
+    // about as long as it computes: 150 -> see DESIGN 3.6)
+    T ln = (T)0, qk = (T)0, lk = (T)0, rk = (T)0, ln_1 = (T)0, qk_1 = (T)0, lk_1 = (T)0, rk_1 = (T)0;
+    if (item < items) issue(item, 0, ln, qk, lk, rk);
     asm volatile("cp.async.commit_group;" ::: "memory");
-    for (; item < items; item += warps, buf ^= 1) {
-        T ln_n = (T)0, qk_n = (T)0, rk_n = (T)0;
-        if (item + warps < items) issue(item + warps, buf ^ 1, ln_n, qk_n, rk_n);
+    if (item + warps < items) issue(item + warps, 1, ln_1, qk_1, lk_1, rk_1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    for (; item < items; item += warps) {
+        T ln_n = (T)0, qk_n = (T)0, lk_n = (T)0, rk_n = (T)0;
+        const int buf2 = buf >= 1 ? buf - 1 : 2;                  // (buf + 2) mod 3
+        if ((unsigned long long)item + 2ull * warps < items) issue(item + 2 * warps, buf2, ln_n, qk_n, lk_n, rk_n);
         asm volatile("cp.async.commit_group;" ::: "memory");
         const uint32_t prob = item / N_;
         const int k = (int)(item - prob * N_);
         const bool has_next = k + 1 < N;
-        asm volatile("cp.async.wait_group 1;" ::: "memory");      // this item's copies (the group before the one just committed)
+        asm volatile("cp.async.wait_group 2;" ::: "memory");      // this item's copies (the group two before the one just committed)
         __syncwarp();
         const T *Qs = mine + (size_t)buf * slice, *As = Qs + e_bb, *Bs = As + e_bb, *Rs = Bs + e_xu;
         T tx = (T)0, tu = (T)0;
@@ -677,7 +683,7 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) schur_recover_s
             }
             tx = s; tu = s2;
         }
-        tx = qk - tx;
+        tx = (qk + lk) - tx;
         tu = rk - tu;
         T sx = (T)0;
 #pragma unroll
@@ -689,8 +695,10 @@ __global__ void __launch_bounds__(256, (sizeof(T) == 4 ? 4 : 2)) schur_recover_s
             for (int p = 0; p < nu; p++) su += Rs[p * nu + lu] * __shfl_sync(0xffffffffu, tu, p);
             if (lane < nu) u[((size_t)item - prob) * nu + lane] = -su;
         }
-        __syncwarp();                                             // the slice is free for the item after next
-        ln = ln_n; qk = qk_n; rk = rk_n;
+        __syncwarp();                                             // the slice is free again
+        ln = ln_1; qk = qk_1; lk = lk_1; rk = rk_1;
+        ln_1 = ln_n; qk_1 = qk_n; lk_1 = lk_n; rk_1 = rk_n;
+        buf = buf == 2 ? 0 : buf + 1;
     }
     asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
