@@ -297,6 +297,34 @@ def test_one_barrier_grid_kernel_pinv_in_shared_memory(nx, nu, N, dt, monkeypatc
     assert it2 == it and np.array_equal(lam2, lam)
 
 
+def test_one_barrier_grid_kernel_deterministic_from_two_streams():
+    """The exchange buffers of pcg_grid1_kernel alternate with the iteration's parity and every launch has its own scratch from the pool:
+    the same system solved 40 times, every other round from two streams at once, gives the same bits every time
+    (scripts/stress_grid.py is the long form)."""
+    torch = _torch()
+    nx, nu, N, dt, tol = 14, 7, 1041, np.float32, 1e-6
+    S, P, gam = g.synth.lqr_schur(nx, nu, N, 3, "stair", dt)
+    d_S, d_P, d_g = (torch.from_numpy(a).cuda() for a in (S, P, gam))
+    cfg = g.pcg_config(pcg_exit_tol=tol, pcg_max_iter=5000, empty_pinv=0)
+    assert "pcg_grid1" in g.plan_query(nx, N, dt, True, cfg)["kernel"]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    outs = [(torch.zeros(N * nx, dtype=torch.float32, device="cuda"), torch.zeros(1, dtype=torch.int32, device="cuda")) for _ in streams]
+    ref = None
+    for r in range(40):
+        n = 2 if r % 2 else 1
+        for (d_l, d_it), st in list(zip(outs, streams))[:n]:
+            with torch.cuda.stream(st):
+                d_l.zero_()
+                g.solve_dev_async(nx, N, d_S, d_P, d_g, d_l, cfg, d_it, None)
+        torch.cuda.synchronize()
+        for d_l, d_it in outs[:n]:
+            cur = (d_l.cpu().numpy(), int(d_it.item()))
+            if ref is None:
+                ref = cur
+            assert cur[1] == ref[1] and np.array_equal(cur[0], ref[0])
+    assert ref[1] > 5
+
+
 def test_grid_kernel_semantics_and_batch():
     """max_iter = 0 leaves lambda; a low cap reports the flag; warm start; a batch of large systems (solved one after the other on
     the same cooperative grid) equals the single solves; NaN-poisoned padding blocks never reach the arithmetic."""
