@@ -38,6 +38,8 @@ sys.path.insert(0, ROOT)
 NX, NU, N_KNOT, DTYPE, TOL, MAX_ITER = 14, 7, 32, np.float32, 1e-6, 1000
 PRECOND = "stair"
 BATCH = 8192
+# systems beyond one 16-CTA cluster, timed in both arms (oracle/Makefile builds the reference harness for exactly these)
+BEYOND_CLUSTER = {"N1500_f32": (14, 7, 1500, np.float32, 1e-6, 5000), "N1000_f64": (14, 7, 1000, np.float64, 1e-10, 5000)}
 
 
 def peaks():
@@ -517,6 +519,20 @@ def single_gpu_extras(torch, g, _lib, S, P, gam, cfg, cfg_build, d_S, d_P, d_it,
         other[name] = {"nx": onx, "knot_points": oN, "dtype": np.dtype(odt).name, "iters": int(di.item()), "kernel_p50_us": pct(lat, 0.5),
                        "kernel_p99_us": pct(lat, 0.99), "cluster": oplan["cluster"], "threads": oplan["threads"]}
 
+    # ---- beyond one 16-CTA cluster (the cooperative-grid kernel): single-solve latency, kernel scope ----
+    for name, (onx, onu, oN, odt, otol, omax) in BEYOND_CLUSTER.items():
+        So, Po, go = g.synth.lqr_schur(onx, onu, oN, 0, "stair", odt)
+        dS, dP, dg = (torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in (So, Po, go))
+        dl = torch.zeros(oN * onx, dtype=dS.dtype, device="cuda")
+        di = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ocfg = g.pcg_config(pcg_exit_tol=otol, pcg_max_iter=omax, empty_pinv=0)
+        lat = time_single_solves(torch, lambda: g.solve_dev_async(onx, oN, dS, dP, dg, dl, ocfg, di, None), dl, n_warm=10, n_timed=60)
+        oplan = g.plan_query(onx, oN, odt, True, ocfg)
+        other[name] = {"nx": onx, "knot_points": oN, "dtype": np.dtype(odt).name, "iters": int(di.item()), "kernel_p50_us": pct(lat, 0.5),
+                       "kernel_p99_us": pct(lat, 0.99), "us_per_iteration": pct(lat, 0.5) / max(int(di.item()), 1),
+                       "kernel": oplan["kernel"], "ctas": oplan["cluster"], "threads": oplan["threads"]}
+        del dS, dP, dg, dl
+
     # ---- fp64 batch: 2048 x C3 (nx 14, N 64, fp64, tol 1e-10, stair), 64 distinct seeds tiled ----
     from gbd_pcg_b200 import layout
     onx, onu, oN, odt, otol, omax = g.synth.CONFIGS["C3"]
@@ -784,6 +800,20 @@ def run_reference(args):
         lat = time_single_solves(torch, lambda: rk.launch(dS, dP, dg, dl, omax, otol), dl, n_warm=20, n_timed=200)
         other[name] = {"nx": onx, "knot_points": oN, "dtype": np.dtype(odt).name, "iters": int(rk.d_iters.item()), "kernel_p50_us": pct(lat, 0.5),
                        "kernel_p99_us": pct(lat, 0.99), **rk.attrs()}
+
+    for name, (onx, onu, oN, odt, otol, omax) in BEYOND_CLUSTER.items():
+        if not ref_cuda.has(odt, onx, oN):
+            other[name] = {"unavailable": f"oracle/_ref/libref_pcg_{'f64' if np.dtype(odt) == np.float64 else 'f32'}_{onx}_{oN}.so not built"}
+            continue
+        So, Po, go = synth.lqr_schur(onx, onu, oN, 0, "stair", odt)
+        rk = ref_cuda.get(odt, onx, oN)
+        dS, dP, dg = (torch.from_numpy(np.ascontiguousarray(x)).cuda() for x in (So, Po, go))
+        dl = torch.zeros(oN * onx, dtype=dS.dtype, device="cuda")
+        lat = time_single_solves(torch, lambda: rk.launch(dS, dP, dg, dl, omax, otol), dl, n_warm=10, n_timed=60)
+        its = int(rk.d_iters.item())
+        other[name] = {"nx": onx, "knot_points": oN, "dtype": np.dtype(odt).name, "iters": its, "kernel_p50_us": pct(lat, 0.5),
+                       "kernel_p99_us": pct(lat, 0.99), "us_per_iteration": pct(lat, 0.5) / max(its, 1), **rk.attrs()}
+        del dS, dP, dg, dl
 
     cores = os.cpu_count() or 1
     ns = min(sample, 2048)
